@@ -1,0 +1,326 @@
+// abi.cu -- the C ABI: the seven legacy libsort symbols (include/libsort.h,
+// reference libsort/libsort.h:12-47) and the additive device-pointer entry
+// points (include/libsort_b200.h).
+//
+// This file deliberately does NOT include libsort.h: the legacy symbols are
+// DEFINED here as returning `int` (0/1 in the whole of eax) while the header
+// declares them `bool`.  Both are returned in al on x86-64/aarch64, so C, C++
+// and cgo callers see a bool, and ctypes callers that never set restype
+// (reference faasTest/pylibsort/sort.py:101,118 read a c_int) see clean upper
+// bits.
+#include <algorithm>
+#include <atomic>
+#include <condition_variable>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+#include <cuda_profiler_api.h>
+#include <cuda_runtime.h>
+
+#include "engine.cuh"
+#include "host_copy.h"
+
+using namespace b200sort;
+
+#define API extern "C" __attribute__((visibility("default")))
+
+namespace {
+
+// ---- device pool (reference libsort/utils.cu:6-61, utils.h:19-68) ----------
+// A counting semaphore over the GPUs plus one busy flag per GPU; a caller
+// blocks while every GPU is taken and gets exclusive use of one otherwise.
+struct DeviceCtx {
+    int dev = -1;
+    bool busy = false;
+    cudaStream_t stream = nullptr;
+    uint32_t *a = nullptr, *b = nullptr;
+    size_t cap_keys = 0;
+    void *ws = nullptr;
+    size_t ws_cap = 0;
+    uint32_t *d_bounds = nullptr;
+    size_t bounds_cap = 0;
+    HostCopier copier;
+};
+
+struct Pool {
+    std::mutex mu;
+    std::condition_variable cv;
+    int free_count = 0;
+    std::vector<DeviceCtx> ctx;
+    bool inited = false;
+};
+Pool g_pool;
+
+bool cuda_ok(cudaError_t e, const char *what)
+{
+    if (e == cudaSuccess) return true;
+    fprintf(stderr, "libsort: %s failed: %s\n", what, cudaGetErrorString(e));
+    return false;
+}
+
+// RAII reservation, released on every return path (reference invokers.cu:17).
+struct Reservation {
+    DeviceCtx *c = nullptr;
+    bool acquire()
+    {
+        std::unique_lock<std::mutex> lk(g_pool.mu);
+        if (!g_pool.inited) {
+            fprintf(stderr, "libsort: initLibSort() has not been called\n");
+            return false;
+        }
+        g_pool.cv.wait(lk, [] { return g_pool.free_count > 0; });
+        for (auto &x : g_pool.ctx) {
+            if (!x.busy) {
+                x.busy = true;
+                g_pool.free_count--;
+                c = &x;
+                break;
+            }
+        }
+        lk.unlock();
+        if (!c) {
+            fprintf(stderr, "libsort: no free device after semaphore (this should not happen)\n");
+            return false;
+        }
+        // the device is set on the calling thread, as in utils.cu:49
+        if (!cuda_ok(cudaSetDevice(c->dev), "cudaSetDevice")) return false;
+        if (!c->stream && !cuda_ok(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking), "cudaStreamCreate"))
+            return false;
+        return true;
+    }
+    ~Reservation()
+    {
+        if (!c) return;
+        {
+            std::lock_guard<std::mutex> lk(g_pool.mu);
+            c->busy = false;
+            g_pool.free_count++;
+        }
+        g_pool.cv.notify_one();
+    }
+};
+
+void free_ctx_buffers(DeviceCtx &c)
+{
+    if (c.dev < 0) return;
+    cudaSetDevice(c.dev);
+    if (c.a) cudaFree(c.a);
+    if (c.b) cudaFree(c.b);
+    if (c.ws) cudaFree(c.ws);
+    if (c.d_bounds) cudaFree(c.d_bounds);
+    c.a = c.b = nullptr;
+    c.ws = nullptr;
+    c.d_bounds = nullptr;
+    c.cap_keys = c.ws_cap = c.bounds_cap = 0;
+    c.copier.release();
+}
+
+// Per-device cached buffers: steady-state calls allocate nothing (the
+// reference spends most of its API time in cudaMalloc/cudaFree,
+// analysis/libsort8b.csv:15-17).
+bool ensure_capacity(DeviceCtx &c, size_t n, size_t ngroups)
+{
+    if (n > c.cap_keys) {
+        if (c.a) cudaFree(c.a);
+        if (c.b) cudaFree(c.b);
+        c.a = c.b = nullptr;
+        c.cap_keys = 0;
+        size_t cap = (n + 1023) & ~(size_t)1023;
+        if (!cuda_ok(cudaMalloc(&c.a, cap * sizeof(uint32_t)), "cudaMalloc(keys)")) return false;
+        if (!cuda_ok(cudaMalloc(&c.b, cap * sizeof(uint32_t)), "cudaMalloc(keys)")) return false;
+        c.cap_keys = cap;
+    }
+    size_t need = workspace_bytes(n);
+    if (need > c.ws_cap) {
+        if (c.ws) cudaFree(c.ws);
+        c.ws = nullptr;
+        c.ws_cap = 0;
+        if (!cuda_ok(cudaMalloc(&c.ws, need), "cudaMalloc(workspace)")) return false;
+        c.ws_cap = need;
+    }
+    if (ngroups > c.bounds_cap) {
+        if (c.d_bounds) cudaFree(c.d_bounds);
+        c.d_bounds = nullptr;
+        c.bounds_cap = 0;
+        if (!cuda_ok(cudaMalloc(&c.d_bounds, ngroups * sizeof(uint32_t)), "cudaMalloc(boundaries)")) return false;
+        c.bounds_cap = ngroups;
+    }
+    return true;
+}
+
+int boundary_mode_from_env()
+{
+    const char *e = getenv("LIBSORT_BOUNDARIES");
+    if (e && (strcmp(e, "exact") == 0 || strcmp(e, "EXACT") == 0)) return BOUNDS_EXACT;
+    return BOUNDS_REFERENCE;
+}
+
+// Host-pointer sort shared by gpuPartial and providedGpu:
+// reserve -> H2D -> K1/K3 passes -> D2H keys (+ boundaries).
+int host_sort(uint32_t *h_keys, size_t n, uint32_t offset, uint32_t width, uint32_t *h_bounds)
+{
+    Reservation r;
+    if (!r.acquire()) return 0;
+    // the sort internally only supports 32-bit sizes (reference invokers.cu:30-33,54-57)
+    if (n > UINT32_MAX) {
+        fprintf(stderr, "Input array length must be less than 2^32\n");
+        return 0;
+    }
+    if (h_bounds && width > 31) {
+        fprintf(stderr, "libsort: group width %u needs 2^%u boundaries; unsupported\n", width, width);
+        return 0;
+    }
+    DeviceCtx &c = *r.c;
+    const size_t ngroups = h_bounds ? ((size_t)1 << width) : 0;
+    if (n == 0) {
+        if (h_bounds) memset(h_bounds, 0, ngroups * sizeof(uint32_t));
+        return 1;
+    }
+    if (!ensure_capacity(c, n, ngroups)) return 0;
+    if (!c.copier.to_device(c.a, h_keys, n * sizeof(uint32_t), c.stream)) return 0;
+    uint32_t *res = nullptr;
+    cudaError_t e = sort_bits(c.a, c.a, c.b, nullptr, n, offset, width, h_bounds ? c.d_bounds : nullptr,
+                              boundary_mode_from_env(), c.ws, c.ws_cap, c.stream, &res, nullptr);
+    if (!cuda_ok(e, "sort")) return 0;
+    if (!c.copier.to_host(h_keys, res, n * sizeof(uint32_t), c.stream)) return 0;
+    if (h_bounds &&
+        !cuda_ok(cudaMemcpyAsync(h_bounds, c.d_bounds, ngroups * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream),
+                 "cudaMemcpy(boundaries)"))
+        return 0;
+    if (!cuda_ok(cudaStreamSynchronize(c.stream), "cudaStreamSynchronize")) return 0;
+    return 1;
+}
+
+}  // namespace
+
+// ---- legacy ABI -------------------------------------------------------------
+
+// reference libsort/utils.cu:10-32
+API int initLibSort(void)
+{
+    std::lock_guard<std::mutex> lk(g_pool.mu);
+    if (g_pool.inited) {
+        fprintf(stderr, "Libsort: attempted to initialize multiple times!\n");
+        return 0;
+    }
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess) {
+        fprintf(stderr, "Failed to get device count (%d): %s\n", ndev, cudaGetErrorString(e));
+        return 0;
+    }
+    if (const char *lim = getenv("LIBSORT_DEVICES")) {
+        int v = atoi(lim);
+        if (v > 0 && v < ndev) ndev = v;
+    }
+    g_pool.ctx.resize(ndev);
+    for (int i = 0; i < ndev; i++) g_pool.ctx[i].dev = i;
+    g_pool.free_count = ndev;
+    g_pool.inited = true;
+    return 1;
+}
+
+// reference libsort/invokers.cu:15-41
+API int gpuPartial(uint32_t *h_in, uint32_t *boundaries, size_t h_in_len, uint32_t offset, uint32_t width)
+{
+    return host_sort(h_in, h_in_len, offset, width, boundaries);
+}
+
+// reference libsort/invokers.cu:45-64
+API int providedGpu(unsigned int *h_in, size_t len) { return host_sort(h_in, len, 0, 32, nullptr); }
+
+// reference libsort/invokers.cu:68-71
+API int providedCpu(unsigned int *in, size_t len)
+{
+    std::sort(in, in + len);
+    return 1;
+}
+
+// reference libsort/utils.cu:63-79 -- PCG-XSH-RR 64/32, process-wide state
+API void populateInput(uint32_t *arr, size_t nelem)
+{
+    static uint64_t state = 0x4d595df4d0f33173ull;
+    uint64_t s = state;
+    for (size_t i = 0; i < nelem; i++) {
+        const uint64_t old = s;
+        s = old * 6364136223846793005ull + 1442695040888963407ull;
+        const uint32_t xorshifted = (uint32_t)((old ^ (old >> 18)) >> 27);
+        const uint32_t rot = (uint32_t)(old >> 59);
+        arr[i] = (xorshifted >> rot) | (xorshifted << ((0u - rot) & 31u));
+    }
+    state = s;
+}
+
+// reference libsort/invokers.cu:73-85
+API int gpuPartialProfile(uint32_t *h_in, uint32_t *boundaries, size_t h_in_len, uint32_t offset, uint32_t width)
+{
+    cudaProfilerStart();
+    int ret = gpuPartial(h_in, boundaries, h_in_len, offset, width);
+    cudaProfilerStop();
+    return ret;
+}
+
+API int providedGpuProfile(unsigned int *h_in, size_t h_in_len)
+{
+    cudaProfilerStart();
+    int ret = providedGpu(h_in, h_in_len);
+    cudaProfilerStop();
+    return ret;
+}
+
+// ---- additive ABI (include/libsort_b200.h) -----------------------------------
+
+struct LibsortKernelTimes {
+    float memset_ms, histogram_ms, scan_ms, pass_ms[4], boundaries_ms;
+    int npass, launches;
+};
+static_assert(sizeof(LibsortKernelTimes) == sizeof(KernelTimes), "ABI struct mirrors engine struct");
+
+API int libsortTileKeys(void) { return tile_keys(); }
+API size_t libsortWorkspaceBytes(size_t n) { return workspace_bytes(n); }
+
+API int libsortDeviceSort(const uint32_t *d_in, uint32_t *d_out, uint32_t *d_tmp, size_t n, uint32_t offset,
+                          uint32_t width, uint32_t *d_boundaries, int boundary_mode, void *d_workspace,
+                          size_t workspace_len, void *stream, LibsortKernelTimes *times)
+{
+    if (n > UINT32_MAX) return -1;
+    if (n && (!d_in || !d_out)) return -1;
+    if (d_tmp == d_out || (d_tmp && d_tmp == d_in)) return -1;
+    uint32_t *res = nullptr;
+    cudaError_t e = sort_bits(d_in, d_out, d_tmp, d_out, n, offset, width, d_boundaries, boundary_mode, d_workspace,
+                              workspace_len, (cudaStream_t)stream, &res, reinterpret_cast<KernelTimes *>(times));
+    return (int)e;
+}
+
+API int libsortDeviceCount(void)
+{
+    std::lock_guard<std::mutex> lk(g_pool.mu);
+    return g_pool.inited ? (int)g_pool.ctx.size() : 0;
+}
+
+API void libsortReleaseCaches(void)
+{
+    std::unique_lock<std::mutex> lk(g_pool.mu);
+    if (!g_pool.inited) return;
+    int prev = 0;
+    cudaGetDevice(&prev);
+    for (auto &c : g_pool.ctx)
+        if (!c.busy) free_ctx_buffers(c);
+    cudaSetDevice(prev);
+}
+
+API const char *libsortErrorString(int code)
+{
+    if (code == 0) return "success";
+    if (code == -1) return "invalid argument";
+    if (code == -2) return "initLibSort has not succeeded";
+    if (code == -3) return "out of memory";
+    if (code > 0) return cudaGetErrorString((cudaError_t)code);
+    return "unknown libsort error";
+}
+
+API void libsortDebugSetPortionTiles(uint32_t tiles) { debug_set_portion_tiles(tiles); }

@@ -1,0 +1,292 @@
+// engine.cu -- see engine.cuh.
+#include "engine.cuh"
+#include "kernels.cuh"
+
+#include <algorithm>
+#include <atomic>
+#include <cstdio>
+#include <cstdlib>
+#include <mutex>
+
+namespace b200sort {
+
+// ---- compiled-in kernel variant -------------------------------------------
+#ifndef SORT_THREADS
+#define SORT_THREADS 512
+#endif
+#ifndef SORT_KPT
+#define SORT_KPT 16
+#endif
+#ifndef SORT_MINB
+#define SORT_MINB 2
+#endif
+#ifndef HIST_THREADS
+#define HIST_THREADS 512
+#endif
+#ifndef HIST_REPL
+#define HIST_REPL 2
+#endif
+
+constexpr int kTile = SORT_THREADS * SORT_KPT;
+using SortSmem = OnesweepSmem<SORT_THREADS, SORT_KPT>;
+
+int tile_keys() { return kTile; }
+
+// workspace layout, in uint32 words
+constexpr size_t WS_HIST = 0;                                   // [4][256]
+constexpr size_t WS_BASE = WS_HIST + MAX_PASSES * RADIX;        // [2][4][256]
+constexpr size_t WS_TICKET = WS_BASE + 2 * MAX_PASSES * RADIX;  // [4 passes][8 portions]
+constexpr size_t WS_DESC = WS_TICKET + 64;                      // [4][ntiles][256]
+constexpr int MAX_PORTIONS = 8;
+
+static std::atomic<uint32_t> g_portion_tiles{0};
+void debug_set_portion_tiles(uint32_t tiles) { g_portion_tiles.store(tiles); }
+
+static uint32_t portion_tiles()
+{
+    uint32_t t = g_portion_tiles.load();
+    return t ? t : (uint32_t)(((1u << 30) - 1) / kTile);
+}
+
+static size_t num_tiles(size_t n) { return (n + kTile - 1) / kTile; }
+
+size_t workspace_bytes(size_t n)
+{
+    return (WS_DESC + (size_t)MAX_PASSES * num_tiles(n) * RADIX) * sizeof(uint32_t);
+}
+
+// ---- per-device launch parameters -----------------------------------------
+struct DevInfo {
+    bool ready = false;
+    int sms = 0;
+    int sort_occ = 0;
+    int hist_occ = 0;
+};
+static DevInfo g_dev[64];
+static std::mutex g_dev_mu;
+
+template <int NPASS>
+static void launch_hist(const uint32_t *in, size_t n, const PassPlan &plan, uint32_t *ghist, int grid, cudaStream_t st)
+{
+    k_histogram<NPASS, HIST_THREADS, HIST_REPL><<<grid, HIST_THREADS, 0, st>>>(in, n, plan, ghist);
+}
+
+static cudaError_t dev_info(DevInfo **out)
+{
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lk(g_dev_mu);
+    DevInfo &d = g_dev[dev];
+    if (!d.ready) {
+        e = cudaDeviceGetAttribute(&d.sms, cudaDevAttrMultiProcessorCount, dev);
+        if (e != cudaSuccess) return e;
+        auto kern = k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB>;
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem));
+        if (e != cudaSuccess) return e;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.sort_occ, kern, SORT_THREADS, sizeof(SortSmem));
+        if (e != cudaSuccess) return e;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.hist_occ, k_histogram<4, HIST_THREADS, HIST_REPL>,
+                                                          HIST_THREADS, 0);
+        if (e != cudaSuccess) return e;
+        if (d.sort_occ < 1 || d.hist_occ < 1) return cudaErrorLaunchOutOfResources;
+        if (const char *dbg = getenv("LIBSORT_DEBUG"))
+            if (dbg[0] == '1')
+                fprintf(stderr, "libsort: dev %d sms=%d tile=%d sort_occ=%d hist_occ=%d smem=%zu\n", dev, d.sms, kTile,
+                        d.sort_occ, d.hist_occ, sizeof(SortSmem));
+        d.ready = true;
+    }
+    *out = &d;
+    return cudaSuccess;
+}
+
+static PassPlan make_plan(uint32_t offset, uint32_t width)
+{
+    // SortState::Step walks 2-bit digits from `offset` while shift < offset+width
+    // (reference sort.cu:323); shifts >= 32 see digit 0 and are identity passes.
+    PassPlan p{};
+    if (offset >= 32) return p;
+    uint64_t eff = ((uint64_t)width + 1) & ~1ull;
+    if (eff > 32 - offset) eff = 32 - offset;
+    uint32_t done = 0;
+    while (done < eff) {
+        uint32_t bits = std::min<uint32_t>(8, (uint32_t)eff - done);
+        p.shift[p.npass] = offset + done;
+        p.mask[p.npass] = (1u << bits) - 1;
+        p.npass++;
+        done += bits;
+    }
+    return p;
+}
+
+struct Timer {
+    cudaStream_t st;
+    bool on;
+    cudaEvent_t ev[16];
+    int n = 0;
+    Timer(cudaStream_t s, bool enable) : st(s), on(enable) {}
+    void mark()
+    {
+        if (!on) return;
+        cudaEventCreate(&ev[n]);
+        cudaEventRecord(ev[n], st);
+        n++;
+    }
+    float span(int i)
+    {
+        float ms = 0;
+        cudaEventElapsedTime(&ms, ev[i], ev[i + 1]);
+        return ms;
+    }
+    ~Timer()
+    {
+        for (int i = 0; i < n; i++) cudaEventDestroy(ev[i]);
+    }
+};
+
+#define CK(x)                                \
+    do {                                     \
+        cudaError_t e_ = (x);                \
+        if (e_ != cudaSuccess) return e_;    \
+    } while (0)
+
+// Boundaries from the sorted keys: exact by binary search, then (reference
+// mode) the gpu_groups/back-fill transform.
+static cudaError_t finish_bounds(const uint32_t *sorted, size_t n, uint32_t offset, size_t ngroups, uint32_t *d_bounds,
+                                 int bounds_mode, cudaStream_t st, int *launches)
+{
+    const int grid = (int)std::min<size_t>((ngroups + 255) / 256, 4096);
+    k_bounds_search<<<grid, 256, 0, st>>>(sorted, (uint32_t)n, offset >= 32 ? 31 : offset,
+                                          offset >= 32 ? 0 : (uint32_t)(ngroups - 1), d_bounds, ngroups);
+    if (launches) ++*launches;
+    if (bounds_mode == BOUNDS_REFERENCE) {
+        k_bounds_refquirk<<<1, 1024, 0, st>>>(d_bounds, ngroups, (uint32_t)n);
+        if (launches) ++*launches;
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t sort_bits(const uint32_t *in, uint32_t *a, uint32_t *b, uint32_t *want, size_t n, uint32_t offset,
+                      uint32_t width, uint32_t *d_bounds, int bounds_mode, void *workspace, size_t workspace_len,
+                      cudaStream_t st, uint32_t **result, KernelTimes *times)
+{
+    if (n > 0xffffffffull) return cudaErrorInvalidValue;
+    if (d_bounds && width > 31) return cudaErrorInvalidValue;
+    const PassPlan plan = make_plan(offset, width);
+    const int P = plan.npass;
+    const size_t ngroups = (size_t)1 << (width > 31 ? 0 : width);
+    if (times) *times = KernelTimes{};
+
+    uint32_t *res = const_cast<uint32_t *>(in);
+    if (n == 0 || P == 0) {
+        // no key moves (empty input, width 0, or offset past bit 31)
+        if (want && want != in && n) {
+            CK(cudaMemcpyAsync(want, in, n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+            res = want;
+        }
+        if (d_bounds) {
+            if (n == 0) CK(cudaMemsetAsync(d_bounds, 0, ngroups * sizeof(uint32_t), st));
+            else CK(finish_bounds(res, n, offset, ngroups, d_bounds, bounds_mode, st, nullptr));
+        }
+        if (result) *result = res;
+        return cudaGetLastError();
+    }
+    if (workspace_len < workspace_bytes(n) || !workspace) return cudaErrorInvalidValue;
+    if (!a || !b || a == b) return cudaErrorInvalidValue;
+
+    DevInfo *dev = nullptr;
+    CK(dev_info(&dev));
+    uint32_t *ws = static_cast<uint32_t *>(workspace);
+    uint32_t *ghist = ws + WS_HIST, *base = ws + WS_BASE, *tickets = ws + WS_TICKET, *desc = ws + WS_DESC;
+    const size_t ntiles = num_tiles(n);
+    const uint32_t ptiles = portion_tiles();
+    const size_t nportions = (ntiles + ptiles - 1) / ptiles;
+    if (nportions > MAX_PORTIONS) return cudaErrorInvalidValue;
+
+    Timer tm(st, times != nullptr);
+    int launches = 0;
+    tm.mark();
+    CK(cudaMemsetAsync(ws, 0, (WS_DESC + (size_t)P * ntiles * RADIX) * sizeof(uint32_t), st));
+    tm.mark();
+
+    // K1: one upsweep, all digits
+    {
+        const size_t want_ctas = (n / 4 + HIST_THREADS * 4 - 1) / (HIST_THREADS * 4);
+        const int grid = (int)std::max<size_t>(1, std::min<size_t>((size_t)dev->sms * dev->hist_occ, want_ctas));
+        switch (P) {
+            case 1: launch_hist<1>(in, n, plan, ghist, grid, st); break;
+            case 2: launch_hist<2>(in, n, plan, ghist, grid, st); break;
+            case 3: launch_hist<3>(in, n, plan, ghist, grid, st); break;
+            default: launch_hist<4>(in, n, plan, ghist, grid, st); break;
+        }
+        launches++;
+    }
+    tm.mark();
+    const bool bounds_from_hist = d_bounds && P == 1 && plan.mask[0] == ngroups - 1;
+    k_scan_hist<<<P, RADIX, 0, st>>>(ghist, base, bounds_from_hist ? d_bounds : nullptr, (uint32_t)ngroups);
+    launches++;
+    tm.mark();
+
+    // pick the ping-pong order
+    uint32_t *dst;
+    if (in == a) dst = b;
+    else if (in == b) dst = a;
+    else {
+        uint32_t *last = want ? want : a;
+        if (last != a && last != b) last = a;
+        dst = (P & 1) ? last : (last == a ? b : a);
+    }
+    const uint32_t *src = in;
+    const bool aligned = true;
+    for (int p = 0; p < P; p++) {
+        const int use_tma = aligned && ((reinterpret_cast<uintptr_t>(src) & 15u) == 0);
+        for (size_t q = 0; q < nportions; q++) {
+            const size_t t0 = q * ptiles, t1 = std::min(ntiles, t0 + ptiles);
+            const size_t k0 = t0 * kTile, k1 = std::min(n, t1 * (size_t)kTile);
+            const uint32_t nt = (uint32_t)(t1 - t0);
+            const int grid = (int)std::min<size_t>(nt, (size_t)dev->sms * dev->sort_occ);
+            uint32_t *bcur = base + ((q & 1) * MAX_PASSES + p) * RADIX;
+            uint32_t *bnext = (q + 1 < nportions) ? base + (((q + 1) & 1) * MAX_PASSES + p) * RADIX : nullptr;
+            k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB><<<grid, SORT_THREADS, sizeof(SortSmem), st>>>(
+                src + k0, dst, (uint32_t)(k1 - k0), plan.shift[p], plan.mask[p], bcur, bnext,
+                desc + ((size_t)p * ntiles + t0) * RADIX, tickets + p * MAX_PORTIONS + q, nt, use_tma);
+            launches++;
+        }
+        tm.mark();
+        src = dst;
+        dst = (dst == a) ? b : a;
+    }
+    res = const_cast<uint32_t *>(src);
+    if (want && res != want) {
+        CK(cudaMemcpyAsync(want, res, n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+        res = want;
+    }
+
+    if (d_bounds) {
+        if (bounds_from_hist) {
+            if (bounds_mode == BOUNDS_REFERENCE) {
+                k_bounds_refquirk<<<1, 1024, 0, st>>>(d_bounds, ngroups, (uint32_t)n);
+                launches++;
+            }
+        } else {
+            CK(finish_bounds(res, n, offset, ngroups, d_bounds, bounds_mode, st, &launches));
+        }
+    }
+    tm.mark();
+    CK(cudaGetLastError());
+    if (result) *result = res;
+    if (times) {
+        CK(cudaStreamSynchronize(st));
+        times->memset_ms = tm.span(0);
+        times->histogram_ms = tm.span(1);
+        times->scan_ms = tm.span(2);
+        for (int p = 0; p < P; p++) times->pass_ms[p] = tm.span(3 + p);
+        times->boundaries_ms = tm.span(3 + P);
+        times->npass = P;
+        times->launches = launches;
+    }
+    return cudaSuccess;
+}
+
+}  // namespace b200sort

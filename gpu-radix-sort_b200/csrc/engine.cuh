@@ -1,0 +1,49 @@
+// engine.cuh -- pass driver over the sm_100a kernels (device-resident data).
+// Replaces SortState::{Step,GetBoundaries} (reference libsort/sort.cu:322-394).
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace b200sort {
+
+enum BoundaryMode : int {
+    BOUNDS_REFERENCE = 0,  // bit-exact with the reference's gpu_groups + back-fill
+    BOUNDS_EXACT = 1,      // exclusive prefix sums of the group histogram
+};
+
+struct KernelTimes {        // milliseconds, filled when requested
+    float memset_ms;
+    float histogram_ms;
+    float scan_ms;
+    float pass_ms[4];
+    float boundaries_ms;
+    int npass;
+    int launches;           // kernels launched by this call
+};
+
+// Keys per scatter tile of the compiled-in kernel variant.
+int tile_keys();
+
+// Scratch bytes needed to sort n keys (histograms, bucket bases, tile
+// tickets, look-back descriptors).
+size_t workspace_bytes(size_t n);
+
+// Stable sort of `in` by bits [offset, offset + 2*ceil(width/2)) -- the net
+// effect of SortState::Step(offset,width) -- using `a` and `b` (n keys each)
+// as ping-pong buffers; `in` may be `a` or `b`, or a third read-only buffer.
+// *result receives the buffer (a or b, or `in` itself when no pass is needed)
+// that holds the sorted keys when the stream reaches this point; if `want` is
+// non-null the result is forced into `want` (one extra device copy when the
+// pass parity does not land there).  d_bounds (nullable, 1<<width entries)
+// receives the group boundaries.  All work is enqueued on `stream`; nothing
+// synchronises unless `times` is non-null.
+cudaError_t sort_bits(const uint32_t *in, uint32_t *a, uint32_t *b, uint32_t *want, size_t n, uint32_t offset,
+                      uint32_t width, uint32_t *d_bounds, int bounds_mode, void *workspace, size_t workspace_len,
+                      cudaStream_t stream, uint32_t **result, KernelTimes *times);
+
+// Test hook: cap the number of tiles per look-back portion (0 = default,
+// i.e. the largest portion whose key count fits the 30-bit descriptors).
+void debug_set_portion_tiles(uint32_t tiles);
+
+}  // namespace b200sort

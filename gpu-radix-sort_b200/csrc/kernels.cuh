@@ -1,0 +1,377 @@
+// kernels.cuh -- the sm_100a kernels of the sort hot path.
+//
+//   K1  k_histogram      one upsweep over the keys, 128-bit streaming loads,
+//                        digit histograms for ALL passes at once (4 B/key).
+//       k_scan_hist      256-bin exclusive scans -> global bucket bases
+//                        (and, for width <= 8, the exact boundaries).
+//   K3  k_onesweep       one stable digit-scatter pass (8 B/key): 1-D bulk TMA
+//                        stages each key tile in shared memory (double
+//                        buffered, persistent CTAs, dynamic tile tickets),
+//                        __match_any_sync ranks keys, keys are re-ordered in
+//                        shared memory and written coalesced per bucket.
+//   K2  (inside K3)      chained scan with decoupled look-back over per-tile
+//                        bucket counts; replaces the reference's multi-kernel
+//                        Blelloch scan (libsort/scan.cu:16-250).
+//       k_bounds_*       boundaries for wide groups / reference quirk mode.
+//
+// Together K1+K3 replace gpu_radix_sort_local, sum_scan_blelloch and
+// gpu_glbl_shuffle (reference libsort/sort.cu:29-213, scan.cu) and k_bounds_*
+// replace gpu_groups + the host back-fill (sort.cu:14-27, 367-394).
+#pragma once
+#include "ptx.cuh"
+
+namespace b200sort {
+
+constexpr int RADIX = 256;       // bins per pass (8-bit digits)
+constexpr int MAX_PASSES = 4;    // 32 bits / 8
+constexpr uint32_t DESC_AGG = 1u << 30;   // tile aggregate published
+constexpr uint32_t DESC_INCL = 2u << 30;  // inclusive prefix published
+constexpr uint32_t DESC_VAL = (1u << 30) - 1;
+
+struct PassPlan {
+    int npass;
+    uint32_t shift[MAX_PASSES];
+    uint32_t mask[MAX_PASSES];
+};
+
+__device__ __forceinline__ uint32_t digit_of(uint32_t key, uint32_t shift, uint32_t mask)
+{
+    return (key >> shift) & mask;
+}
+
+// ---------------------------------------------------------------- K1 ------
+// Grid: persistent, a multiple of the SM count.  Each CTA keeps NPASS x 256
+// counters per replica in shared memory; warps are spread over REPL replicas
+// to thin out same-address atomic collisions.  Flushed once per CTA.
+template <int NPASS, int THREADS, int REPL>
+__global__ void __launch_bounds__(THREADS) k_histogram(const uint32_t *__restrict__ in, size_t n, PassPlan plan,
+                                                      uint32_t *__restrict__ ghist)
+{
+    __shared__ uint32_t s_hist[REPL][NPASS][RADIX];
+    for (int i = threadIdx.x; i < REPL * NPASS * RADIX; i += THREADS) (&s_hist[0][0][0])[i] = 0;
+    __syncthreads();
+
+    uint32_t(*my)[RADIX] = s_hist[(threadIdx.x >> 5) % REPL];
+    uint32_t shift[NPASS], mask[NPASS];
+#pragma unroll
+    for (int p = 0; p < NPASS; p++) { shift[p] = plan.shift[p]; mask[p] = plan.mask[p]; }
+
+    auto count = [&](uint32_t k) {
+#pragma unroll
+        for (int p = 0; p < NPASS; p++) atomicAdd(&my[p][digit_of(k, shift[p], mask[p])], 1u);
+    };
+
+    // scalar head up to the first 16 B boundary, vector body, scalar tail
+    size_t head = ((16u - (reinterpret_cast<uintptr_t>(in) & 15u)) & 15u) >> 2;
+    if (head > n) head = n;
+    const size_t nvec = (n - head) >> 2;
+    const size_t tail0 = head + (nvec << 2);
+    const size_t gtid = (size_t)blockIdx.x * THREADS + threadIdx.x;
+    const size_t gstride = (size_t)gridDim.x * THREADS;
+    if (gtid < head) count(in[gtid]);
+    if (gtid < n - tail0) count(in[tail0 + gtid]);
+
+    const uint4 *vin = reinterpret_cast<const uint4 *>(in + head);
+    constexpr int U = 4;
+    size_t i = gtid;
+    for (; i + (U - 1) * gstride < nvec; i += U * gstride) {
+        uint4 v[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) v[u] = ld_stream_v4(vin + i + u * gstride);
+#pragma unroll
+        for (int u = 0; u < U; u++) { count(v[u].x); count(v[u].y); count(v[u].z); count(v[u].w); }
+    }
+    for (; i < nvec; i += gstride) {
+        uint4 v = ld_stream_v4(vin + i);
+        count(v.x); count(v.y); count(v.z); count(v.w);
+    }
+    __syncthreads();
+    for (int j = threadIdx.x; j < NPASS * RADIX; j += THREADS) {
+        uint32_t c = 0;
+#pragma unroll
+        for (int r = 0; r < REPL; r++) c += (&s_hist[r][0][0])[j];
+        if (c) atomicAdd(&ghist[j], c);
+    }
+}
+
+// 256-thread block-wide exclusive scan helper (threads >= 256 pass 0 / ignore).
+__device__ __forceinline__ uint32_t block_excl_scan_256(uint32_t v, uint32_t *s_warp /*>=8*/, uint32_t *total)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31 && warp < 8) s_warp[warp] = inc;
+    __syncthreads();
+    uint32_t wbase = 0, tot = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++) {
+        uint32_t c = s_warp[w];
+        if (w < warp) wbase += c;
+        tot += c;
+    }
+    if (total) *total = tot;
+    return wbase + inc - v;
+}
+
+// One 256-thread CTA per pass: base[p][b] = #keys whose digit p is < b.
+// When d_exact != nullptr (single-pass partial sort, width <= 8) the scan of
+// pass 0 IS the exact boundary array (localTest/tests.cpp:44-54).
+__global__ void __launch_bounds__(256) k_scan_hist(const uint32_t *__restrict__ ghist, uint32_t *__restrict__ base,
+                                                  uint32_t *__restrict__ d_exact, uint32_t ngroups)
+{
+    __shared__ uint32_t s_warp[8];
+    const int p = blockIdx.x;
+    uint32_t c = ghist[p * RADIX + threadIdx.x];
+    uint32_t ex = block_excl_scan_256(c, s_warp, nullptr);
+    base[p * RADIX + threadIdx.x] = ex;
+    if (d_exact && p == 0 && threadIdx.x < ngroups) d_exact[threadIdx.x] = ex;
+}
+
+// ---------------------------------------------------------------- K3 ------
+template <int THREADS, int KPT>
+struct OnesweepSmem {
+    static constexpr int TILE = THREADS * KPT;
+    static constexpr int NWARPS = THREADS / 32;
+    alignas(128) uint32_t keys[2][TILE];       // TMA destinations, re-used for the sorted tile
+    uint32_t warp_hist[NWARPS][RADIX];         // per-warp digit counters -> running offsets
+    uint32_t tile_offs[RADIX];                 // global dst of bucket b minus its start in the tile
+    uint32_t s_warp[8];
+    alignas(8) uint64_t mbar[2];
+    uint32_t next_tile[2];
+};
+
+// in/out: this portion's keys (n < 2^30 so that counts fit the 30-bit
+// descriptor value).  base: global bucket bases for this portion;
+// base_next (nullable): receives base + portion bucket totals for the next
+// portion.  desc: ntiles x 256 zero-initialised descriptors; ticket: zeroed.
+template <int THREADS, int KPT, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB)
+    k_onesweep(const uint32_t *__restrict__ in, uint32_t *__restrict__ out, uint32_t n, uint32_t shift, uint32_t mask,
+               const uint32_t *__restrict__ base, uint32_t *__restrict__ base_next, uint32_t *__restrict__ desc,
+               uint32_t *__restrict__ ticket, uint32_t ntiles, int use_tma)
+{
+    using Smem = OnesweepSmem<THREADS, KPT>;
+    constexpr int TILE = Smem::TILE;
+    constexpr int NWARPS = Smem::NWARPS;
+    static_assert(THREADS >= RADIX, "need one thread per bin");
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    Smem &s = *reinterpret_cast<Smem *>(smem_raw);
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t lt = lanemask_lt();
+
+    auto issue_load = [&](uint32_t tile, int buf) {
+        // elected thread: arm the barrier and start the bulk copy of the
+        // 16 B-multiple part of the tile; a ragged tail (<= 3 keys, last tile
+        // only) is read straight from global by its consumer.
+        const uint32_t valid = min((uint32_t)TILE, n - tile * (uint32_t)TILE);
+        const uint32_t bytes = (valid * 4u) & ~15u;
+        if (bytes) {
+            mbar_arrive_expect_tx(&s.mbar[buf], bytes);
+            tma_load_1d(s.keys[buf], in + (size_t)tile * TILE, bytes, &s.mbar[buf]);
+        } else {
+            mbar_arrive_expect_tx(&s.mbar[buf], 0);
+        }
+    };
+
+    if (tid == 0) {
+        mbar_init(&s.mbar[0], 1);
+        mbar_init(&s.mbar[1], 1);
+        fence_mbar_init();
+        uint32_t t = atomicAdd(ticket, 1u);
+        s.next_tile[0] = t;
+        if (use_tma && t < ntiles) issue_load(t, 0);
+    }
+    __syncthreads();
+    uint32_t cur = s.next_tile[0];
+
+    for (uint32_t it = 0; cur < ntiles; ++it) {
+        const int buf = it & 1;
+        const uint32_t tile_base = cur * (uint32_t)TILE;
+        const uint32_t valid = min((uint32_t)TILE, n - tile_base);
+
+        // (1) take the next ticket and prefetch that tile into the other buffer
+        if (tid == 0) {
+            uint32_t t = atomicAdd(ticket, 1u);
+            s.next_tile[buf ^ 1] = t;
+            if (use_tma && t < ntiles) {
+                fence_proxy_async();  // last iteration's generic stores to keys[buf^1] come first
+                issue_load(t, buf ^ 1);
+            }
+        }
+#pragma unroll
+        for (int j = lane; j < RADIX; j += 32) s.warp_hist[warp][j] = 0;
+
+        // (2) keys -> registers, warp-striped so that tile order == rank order
+        uint32_t key[KPT];
+        const uint32_t wbase = warp * (KPT * 32) + lane;
+        if (use_tma) {
+            mbar_wait(&s.mbar[buf], (it >> 1) & 1);
+            if (valid == TILE) {
+#pragma unroll
+                for (int i = 0; i < KPT; i++) key[i] = s.keys[buf][wbase + i * 32];
+            } else {
+                const uint32_t staged = ((valid * 4u) & ~15u) >> 2;
+#pragma unroll
+                for (int i = 0; i < KPT; i++) {
+                    const uint32_t idx = wbase + i * 32;
+                    key[i] = idx < staged ? s.keys[buf][idx] : (idx < valid ? in[(size_t)tile_base + idx] : 0xffffffffu);
+                }
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < KPT; i++) {
+                const uint32_t idx = wbase + i * 32;
+                key[i] = idx < valid ? in[(size_t)tile_base + idx] : 0xffffffffu;
+            }
+        }
+        __syncwarp();
+
+        // (3) early counts: per-warp digit histogram
+#pragma unroll
+        for (int i = 0; i < KPT; i++) atomicAdd(&s.warp_hist[warp][digit_of(key[i], shift, mask)], 1u);
+        __syncthreads();
+
+        // (4) bin threads: reduce over warps, publish the tile aggregate,
+        //     scan bins, turn warp counters into running offsets in the tile
+        uint32_t my_count = 0, my_start = 0;
+        if (tid < RADIX) {
+#pragma unroll
+            for (int w = 0; w < NWARPS; w++) my_count += s.warp_hist[w][tid];
+            uint32_t agg = my_count;
+            if ((uint32_t)tid == mask) agg -= (uint32_t)TILE - valid;  // padding keys carry the top digit
+            st_relaxed(&desc[(size_t)cur * RADIX + tid], (cur == 0 ? DESC_INCL : DESC_AGG) | agg);
+            my_count = agg | 0u;  // keep the unpadded count for the look-back
+        }
+        {
+            uint32_t padded = 0;
+            if (tid < RADIX) {
+                padded = my_count;
+                if ((uint32_t)tid == mask) padded += (uint32_t)TILE - valid;
+            }
+            my_start = block_excl_scan_256(padded, s.s_warp, nullptr);
+        }
+        if (tid < RADIX) {
+            uint32_t run = my_start;
+#pragma unroll
+            for (int w = 0; w < NWARPS; w++) {
+                uint32_t c = s.warp_hist[w][tid];
+                s.warp_hist[w][tid] = run;
+                run += c;
+            }
+        }
+        __syncthreads();
+
+        // (5) rank: position of every key in the digit-sorted tile
+        uint32_t pos[KPT];
+#pragma unroll
+        for (int i = 0; i < KPT; i++) {
+            const uint32_t d = digit_of(key[i], shift, mask);
+            const uint32_t peers = __match_any_sync(0xffffffffu, d);
+            const uint32_t before = __popc(peers & lt);
+            uint32_t off = 0;
+            if (before == 0) off = atomicAdd(&s.warp_hist[warp][d], (uint32_t)__popc(peers));
+            off = __shfl_sync(0xffffffffu, off, __ffs(peers) - 1);
+            pos[i] = off + before;
+        }
+        // every warp has its keys in registers since (3); the staging buffer can be overwritten
+#pragma unroll
+        for (int i = 0; i < KPT; i++) s.keys[buf][pos[i]] = key[i];
+
+        // (6) decoupled look-back for this thread's bin
+        if (tid < RADIX) {
+            uint32_t excl = 0;
+            if (cur != 0) {
+                uint32_t j = cur - 1;
+                while (true) {
+                    uint32_t v = ld_relaxed(&desc[(size_t)j * RADIX + tid]);
+                    if ((v >> 30) == 0) continue;
+                    excl += v & DESC_VAL;
+                    if (v & DESC_INCL) break;
+                    --j;
+                }
+                st_relaxed(&desc[(size_t)cur * RADIX + tid], DESC_INCL | (excl + my_count));
+            }
+            const uint32_t gbase = base[tid];
+            s.tile_offs[tid] = gbase + excl - my_start;
+            if (base_next && cur == ntiles - 1) base_next[tid] = gbase + excl + my_count;
+        }
+        __syncthreads();
+
+        // (7) coalesced write-out: consecutive threads, consecutive sorted keys
+        if (valid == TILE) {
+#pragma unroll
+            for (int i = 0; i < KPT; i++) {
+                const uint32_t p = tid + i * THREADS;
+                const uint32_t k = s.keys[buf][p];
+                out[s.tile_offs[digit_of(k, shift, mask)] + p] = k;
+            }
+        } else {
+            for (uint32_t p = tid; p < valid; p += THREADS) {
+                const uint32_t k = s.keys[buf][p];
+                out[s.tile_offs[digit_of(k, shift, mask)] + p] = k;
+            }
+        }
+        __syncthreads();
+        cur = s.next_tile[buf ^ 1];
+    }
+}
+
+// ------------------------------------------------------------ boundaries --
+// Exact boundaries for wide groups: thread g finds the first index whose
+// group is >= g in the array already sorted by those bits.
+__global__ void k_bounds_search(const uint32_t *__restrict__ sorted, uint32_t n, uint32_t offset, uint32_t gmask,
+                                uint32_t *__restrict__ exact, size_t ngroups)
+{
+    for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g < ngroups; g += (size_t)gridDim.x * blockDim.x) {
+        uint32_t lo = 0, hi = n;
+        while (lo < hi) {
+            uint32_t mid = lo + ((hi - lo) >> 1);
+            if (((sorted[mid] >> offset) & gmask) < (uint32_t)g) lo = mid + 1; else hi = mid;
+        }
+        exact[g] = lo;
+    }
+}
+
+// In place: exact boundaries -> what the reference's gpu_groups + host
+// back-fill produce (libsort/sort.cu:14-27, 381-387).  With g0 the first
+// non-empty group:  R[0] = 0;  R[1] = E[1] iff groups 0 and 1 are both
+// non-empty, else 0;  R[g>=2] = E[g] for g > g0, else E[g0+1] (E[G] = n).
+// Single CTA: the reads of E[g0+1], E[1], E[2] complete before any write.
+__global__ void __launch_bounds__(1024) k_bounds_refquirk(uint32_t *__restrict__ b, size_t ngroups, uint32_t n)
+{
+    __shared__ unsigned long long s_g0;
+    __shared__ uint32_t s_fill, s_r1;
+    if (threadIdx.x == 0) s_g0 = ngroups;
+    __syncthreads();
+    unsigned long long mine = ngroups;
+    for (size_t g = threadIdx.x; g < ngroups; g += blockDim.x) {
+        uint32_t nxt = (g + 1 < ngroups) ? b[g + 1] : n;
+        if (nxt != b[g]) { mine = g; break; }
+    }
+    if (mine < ngroups) atomicMin(&s_g0, mine);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const size_t g0 = s_g0;
+        s_fill = (g0 + 1 < ngroups) ? b[g0 + 1] : n;
+        uint32_t r1 = 0;
+        if (ngroups > 1) {
+            const uint32_t e1 = b[1], e2 = ngroups > 2 ? b[2] : n;
+            if (e1 != 0 && e2 != e1) r1 = e1;  // count[0] > 0 and count[1] > 0
+        }
+        s_r1 = r1;
+    }
+    __syncthreads();
+    const size_t g0 = s_g0;
+    for (size_t g = threadIdx.x; g < ngroups; g += blockDim.x) {
+        if (g == 0) b[0] = 0;
+        else if (g == 1) b[1] = s_r1;
+        else if (g <= g0) b[g] = s_fill;
+    }
+}
+
+}  // namespace b200sort
