@@ -65,10 +65,44 @@ struct DevInfo {
 static DevInfo g_dev[64];
 static std::mutex g_dev_mu;
 
-template <int NPASS>
-static void launch_hist(const uint32_t *in, size_t n, const PassPlan &plan, uint32_t *ghist, int grid, cudaStream_t st)
+static int env_int(const char *name, int dflt)
 {
-    k_histogram<NPASS, HIST_THREADS, HIST_REPL><<<grid, HIST_THREADS, 0, st>>>(in, n, plan, ghist);
+    const char *e = getenv(name);
+    return e ? atoi(e) : dflt;
+}
+// 1 = bank-private K1 (one 1024-thread CTA per SM), 0 = replicated K1
+static const int g_hist_mode = env_int("LIBSORT_HIST_MODE", 1);
+
+template <int NPASS>
+static cudaError_t launch_hist(const uint32_t *in, size_t n, const PassPlan &plan, uint32_t *ghist, int sms, int occ,
+                               cudaStream_t st)
+{
+    if (g_hist_mode == 1 && n >= (1u << 16)) {
+        auto kern = k_histogram_lanes<NPASS, 1024>;
+        static std::atomic<bool> attr_set{false};
+        const int smem = NPASS * RADIX * 32 * (int)sizeof(uint32_t);
+        if (!attr_set.load()) {
+            // set on every device the first time through (attribute is per device)
+            int cur = 0, ndev = 0;
+            cudaGetDevice(&cur);
+            cudaGetDeviceCount(&ndev);
+            for (int d = 0; d < ndev; d++) {
+                cudaSetDevice(d);
+                cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+                if (e != cudaSuccess) { cudaSetDevice(cur); return e; }
+            }
+            cudaSetDevice(cur);
+            attr_set.store(true);
+        }
+        const size_t want = (n / 4 + 1024 * 4 - 1) / (1024 * 4);
+        const int grid = (int)std::max<size_t>(1, std::min<size_t>((size_t)sms, want));
+        kern<<<grid, 1024, smem, st>>>(in, n, plan, ghist);
+    } else {
+        const size_t want = (n / 4 + HIST_THREADS * 4 - 1) / (HIST_THREADS * 4);
+        const int grid = (int)std::max<size_t>(1, std::min<size_t>((size_t)sms * occ, want));
+        k_histogram<NPASS, HIST_THREADS, HIST_REPL><<<grid, HIST_THREADS, 0, st>>>(in, n, plan, ghist);
+    }
+    return cudaSuccess;
 }
 
 static cudaError_t dev_info(DevInfo **out)
@@ -82,8 +116,11 @@ static cudaError_t dev_info(DevInfo **out)
     if (!d.ready) {
         e = cudaDeviceGetAttribute(&d.sms, cudaDevAttrMultiProcessorCount, dev);
         if (e != cudaSuccess) return e;
-        auto kern = k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB>;
+        auto kern = k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, 8>;
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem));
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, 0>,
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem));
         if (e != cudaSuccess) return e;
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.sort_occ, kern, SORT_THREADS, sizeof(SortSmem));
         if (e != cudaSuccess) return e;
@@ -211,17 +248,13 @@ cudaError_t sort_bits(const uint32_t *in, uint32_t *a, uint32_t *b, uint32_t *wa
     tm.mark();
 
     // K1: one upsweep, all digits
-    {
-        const size_t want_ctas = (n / 4 + HIST_THREADS * 4 - 1) / (HIST_THREADS * 4);
-        const int grid = (int)std::max<size_t>(1, std::min<size_t>((size_t)dev->sms * dev->hist_occ, want_ctas));
-        switch (P) {
-            case 1: launch_hist<1>(in, n, plan, ghist, grid, st); break;
-            case 2: launch_hist<2>(in, n, plan, ghist, grid, st); break;
-            case 3: launch_hist<3>(in, n, plan, ghist, grid, st); break;
-            default: launch_hist<4>(in, n, plan, ghist, grid, st); break;
-        }
-        launches++;
+    switch (P) {
+        case 1: CK(launch_hist<1>(in, n, plan, ghist, dev->sms, dev->hist_occ, st)); break;
+        case 2: CK(launch_hist<2>(in, n, plan, ghist, dev->sms, dev->hist_occ, st)); break;
+        case 3: CK(launch_hist<3>(in, n, plan, ghist, dev->sms, dev->hist_occ, st)); break;
+        default: CK(launch_hist<4>(in, n, plan, ghist, dev->sms, dev->hist_occ, st)); break;
     }
+    launches++;
     tm.mark();
     const bool bounds_from_hist = d_bounds && P == 1 && plan.mask[0] == ngroups - 1;
     k_scan_hist<<<P, RADIX, 0, st>>>(ghist, base, bounds_from_hist ? d_bounds : nullptr, (uint32_t)ngroups);
@@ -248,7 +281,9 @@ cudaError_t sort_bits(const uint32_t *in, uint32_t *a, uint32_t *b, uint32_t *wa
             const int grid = (int)std::min<size_t>(nt, (size_t)dev->sms * dev->sort_occ);
             uint32_t *bcur = base + ((q & 1) * MAX_PASSES + p) * RADIX;
             uint32_t *bnext = (q + 1 < nportions) ? base + (((q + 1) & 1) * MAX_PASSES + p) * RADIX : nullptr;
-            k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB><<<grid, SORT_THREADS, sizeof(SortSmem), st>>>(
+            auto kern = plan.mask[p] == 0xffu ? k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, 8>
+                                              : k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, 0>;
+            kern<<<grid, SORT_THREADS, sizeof(SortSmem), st>>>(
                 src + k0, dst, (uint32_t)(k1 - k0), plan.shift[p], plan.mask[p], bcur, bnext,
                 desc + ((size_t)p * ntiles + t0) * RADIX, tickets + p * MAX_PORTIONS + q, nt, use_tma);
             launches++;

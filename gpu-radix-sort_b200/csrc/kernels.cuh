@@ -94,6 +94,58 @@ __global__ void __launch_bounds__(THREADS) k_histogram(const uint32_t *__restric
     }
 }
 
+// K1, bank-private layout: counter (pass p, digit d) has 32 copies, copy l in
+// bank l, and lane l only ever touches its own bank, so a warp's 32 shared
+// atomics never collide (random 8-bit digits otherwise cost ~2.35 cycles per
+// warp-op in bank conflicts, which caps a 4-digit histogram below HBM speed).
+// NPASS * 32 KB of dynamic shared memory, one CTA per SM.
+template <int NPASS, int THREADS>
+__global__ void __launch_bounds__(THREADS, 1) k_histogram_lanes(const uint32_t *__restrict__ in, size_t n, PassPlan plan,
+                                                               uint32_t *__restrict__ ghist)
+{
+    extern __shared__ __align__(16) uint32_t s_lane_hist[];  // [NPASS][RADIX][32]
+    for (int i = threadIdx.x; i < NPASS * RADIX * 32; i += THREADS) s_lane_hist[i] = 0;
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31;
+    uint32_t shift[NPASS], mask[NPASS];
+#pragma unroll
+    for (int p = 0; p < NPASS; p++) { shift[p] = plan.shift[p]; mask[p] = plan.mask[p]; }
+    auto count = [&](uint32_t k) {
+#pragma unroll
+        for (int p = 0; p < NPASS; p++)
+            atomicAdd(&s_lane_hist[(p * RADIX + digit_of(k, shift[p], mask[p])) * 32 + lane], 1u);
+    };
+    size_t head = ((16u - (reinterpret_cast<uintptr_t>(in) & 15u)) & 15u) >> 2;
+    if (head > n) head = n;
+    const size_t nvec = (n - head) >> 2;
+    const size_t tail0 = head + (nvec << 2);
+    const size_t gtid = (size_t)blockIdx.x * THREADS + threadIdx.x;
+    const size_t gstride = (size_t)gridDim.x * THREADS;
+    if (gtid < head) count(in[gtid]);
+    if (gtid < n - tail0) count(in[tail0 + gtid]);
+    const uint4 *vin = reinterpret_cast<const uint4 *>(in + head);
+    constexpr int U = 4;
+    size_t i = gtid;
+    for (; i + (U - 1) * gstride < nvec; i += U * gstride) {
+        uint4 v[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) v[u] = ld_stream_v4(vin + i + u * gstride);
+#pragma unroll
+        for (int u = 0; u < U; u++) { count(v[u].x); count(v[u].y); count(v[u].z); count(v[u].w); }
+    }
+    for (; i < nvec; i += gstride) {
+        uint4 v = ld_stream_v4(vin + i);
+        count(v.x); count(v.y); count(v.z); count(v.w);
+    }
+    __syncthreads();
+    for (int j = threadIdx.x; j < NPASS * RADIX; j += THREADS) {
+        uint32_t c = 0;
+#pragma unroll
+        for (int l = 0; l < 32; l++) c += s_lane_hist[j * 32 + ((l + lane) & 31)];
+        if (c) atomicAdd(&ghist[j], c);
+    }
+}
+
 // 256-thread block-wide exclusive scan helper (threads >= 256 pass 0 / ignore).
 __device__ __forceinline__ uint32_t block_excl_scan_256(uint32_t v, uint32_t *s_warp /*>=8*/, uint32_t *total)
 {
@@ -132,6 +184,57 @@ __global__ void __launch_bounds__(256) k_scan_hist(const uint32_t *__restrict__ 
 }
 
 // ---------------------------------------------------------------- K3 ------
+// Lanes of the warp whose digit equals this lane's.  MATCH.ANY costs about two
+// cycles per DISTINCT value on B200 (measured: 62 cycles per warp-op for random
+// 8-bit digits, SM-wide, not per scheduler), so the peer mask is built from one
+// ballot per digit bit instead (VOTE runs at two warp-ops per cycle per SM).
+// MATCH.ANY is kept for the narrow (<= 2-bit) passes where it is cheaper.
+// One digit bit of the ballot match, in PTX so that it stays at four SASS
+// instructions (LOP3 -> predicate, VOTE, SEL, LOP3): peers &= ballot(bit) ^ (bit ? 0 : ~0).
+__device__ __forceinline__ uint32_t match_bit(uint32_t peers, uint32_t d, uint32_t bitmask)
+{
+    asm("{\n\t"
+        ".reg .pred p;\n\t"
+        ".reg .b32 t, m, x;\n\t"
+        "and.b32 t, %1, %2;\n\t"
+        "setp.ne.u32 p, t, 0;\n\t"
+        "vote.sync.ballot.b32 m, p, 0xffffffff;\n\t"
+        "selp.b32 x, 0, -1, p;\n\t"
+        "lop3.b32 %0, %0, m, x, 0x60;\n\t"
+        "}"
+        : "+r"(peers)
+        : "r"(d), "r"(bitmask));
+    return peers;
+}
+
+template <int NBITS>
+__device__ __forceinline__ uint32_t match_digit(uint32_t d, int nbits_rt)
+{
+    if (NBITS == 0 && nbits_rt <= 2) return __match_any_sync(0xffffffffu, d);
+    uint32_t peers = 0xffffffffu;
+#pragma unroll
+    for (int b = 0; b < 8; b++)
+        if (NBITS ? (b < NBITS) : (b < nbits_rt)) peers = match_bit(peers, d, 1u << b);
+    return peers;
+}
+
+// Leader-only shared atomic add without a branch: the highest peer lane adds
+// the group's size to the warp's running digit counter and gets the old value.
+__device__ __forceinline__ uint32_t leader_atom_add(uint32_t smem_addr, uint32_t val, bool leader)
+{
+    uint32_t old = 0;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.u32 p, %3, 0;\n\t"
+        "@p atom.shared.add.u32 %0, [%1], %2;\n\t"
+        "}"
+        : "+r"(old)
+        : "r"(smem_addr), "r"(val), "r"((uint32_t)leader)
+        : "memory");
+    return old;
+}
+
 template <int THREADS, int KPT>
 struct OnesweepSmem {
     static constexpr int TILE = THREADS * KPT;
@@ -148,7 +251,7 @@ struct OnesweepSmem {
 // descriptor value).  base: global bucket bases for this portion;
 // base_next (nullable): receives base + portion bucket totals for the next
 // portion.  desc: ntiles x 256 zero-initialised descriptors; ticket: zeroed.
-template <int THREADS, int KPT, int MINB>
+template <int THREADS, int KPT, int MINB, int NBITS>
 __global__ void __launch_bounds__(THREADS, MINB)
     k_onesweep(const uint32_t *__restrict__ in, uint32_t *__restrict__ out, uint32_t n, uint32_t shift, uint32_t mask,
                const uint32_t *__restrict__ base, uint32_t *__restrict__ base_next, uint32_t *__restrict__ desc,
@@ -163,6 +266,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t lt = lanemask_lt();
+    const int nbits = __popc(mask);
 
     auto issue_load = [&](uint32_t tile, int buf) {
         // elected thread: arm the barrier and start the bulk copy of the
@@ -268,14 +372,15 @@ __global__ void __launch_bounds__(THREADS, MINB)
 
         // (5) rank: position of every key in the digit-sorted tile
         uint32_t pos[KPT];
+        const uint32_t my_hist = smem_u32(&s.warp_hist[warp][0]);
 #pragma unroll
         for (int i = 0; i < KPT; i++) {
             const uint32_t d = digit_of(key[i], shift, mask);
-            const uint32_t peers = __match_any_sync(0xffffffffu, d);
+            const uint32_t peers = match_digit<NBITS>(d, nbits);
             const uint32_t before = __popc(peers & lt);
-            uint32_t off = 0;
-            if (before == 0) off = atomicAdd(&s.warp_hist[warp][d], (uint32_t)__popc(peers));
-            off = __shfl_sync(0xffffffffu, off, __ffs(peers) - 1);
+            const int top = 31 - __clz(peers);  // highest peer lane leads; its `before` + 1 is the group size
+            uint32_t off = leader_atom_add(my_hist + d * 4u, before + 1u, lane == top);
+            off = __shfl_sync(0xffffffffu, off, top);
             pos[i] = off + before;
         }
         // every warp has its keys in registers since (3); the staging buffer can be overwritten
