@@ -1,0 +1,111 @@
+"""ctypes binding of libsort.so (include/libsort.h, include/libsort_b200.h)."""
+import ctypes
+import os
+import subprocess
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_CSRC = os.path.join(_HERE, "csrc")
+_LIBDIR = os.path.join(_HERE, "libsort")
+
+LEGACY_SYMBOLS = ["initLibSort", "gpuPartial", "providedGpu", "providedCpu", "populateInput",
+                  "gpuPartialProfile", "providedGpuProfile"]
+ADDITIVE_SYMBOLS = ["libsortTileKeys", "libsortWorkspaceBytes", "libsortDeviceSort", "libsortDeviceCount",
+                    "libsortReleaseCaches", "libsortErrorString", "libsortDebugSetPortionTiles",
+                    "libsortDeviceHistogram", "libsortDeviceScatterToPeers", "libsortIpcExport", "libsortIpcOpen",
+                    "libsortIpcClose"]
+
+BOUNDS_REFERENCE = 0
+BOUNDS_EXACT = 1
+
+
+class KernelTimes(ctypes.Structure):
+    _fields_ = [("memset_ms", ctypes.c_float), ("histogram_ms", ctypes.c_float), ("scan_ms", ctypes.c_float),
+                ("pass_ms", ctypes.c_float * 4), ("boundaries_ms", ctypes.c_float), ("npass", ctypes.c_int),
+                ("launches", ctypes.c_int)]
+
+
+def lib_path():
+    return os.path.join(_LIBDIR, "libsort.so")
+
+
+def build(verbose=False):
+    """Compile csrc/ for sm_100a into libsort/libsort.so (nvcc; no GPU needed)."""
+    res = subprocess.run(["make", "-C", _CSRC, "all", "tools"], capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("libsort build failed:\n" + res.stdout[-4000:] + res.stderr[-4000:])
+    if verbose:
+        print(res.stdout)
+    return lib_path()
+
+
+_lib = None
+
+
+def lib():
+    """Load libsort.so.  Raises if it is missing: the CUDA library IS the product."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = lib_path()
+    if not os.path.exists(path):
+        raise RuntimeError(
+            "%s not found: build it with `make -C %s` (or __graft_entry__.build()); "
+            "there is no CPU fallback" % (path, _CSRC))
+    L = ctypes.CDLL(path)
+    u32p = ctypes.POINTER(ctypes.c_uint32)
+    vp, sz, u32, ci = ctypes.c_void_p, ctypes.c_size_t, ctypes.c_uint32, ctypes.c_int
+    L.initLibSort.argtypes = []
+    L.initLibSort.restype = ctypes.c_bool
+    for name in ("gpuPartial", "gpuPartialProfile"):
+        f = getattr(L, name)
+        f.argtypes = [vp, vp, sz, u32, u32]
+        f.restype = ctypes.c_bool
+    for name in ("providedGpu", "providedCpu", "providedGpuProfile"):
+        f = getattr(L, name)
+        f.argtypes = [vp, sz]
+        f.restype = ctypes.c_bool
+    L.populateInput.argtypes = [vp, sz]
+    L.populateInput.restype = None
+    L.libsortTileKeys.restype = ci
+    L.libsortWorkspaceBytes.argtypes = [sz]
+    L.libsortWorkspaceBytes.restype = sz
+    L.libsortDeviceSort.argtypes = [vp, vp, vp, sz, u32, u32, vp, ci, vp, sz, vp, ctypes.POINTER(KernelTimes)]
+    L.libsortDeviceSort.restype = ci
+    L.libsortDeviceCount.restype = ci
+    L.libsortReleaseCaches.restype = None
+    L.libsortErrorString.argtypes = [ci]
+    L.libsortErrorString.restype = ctypes.c_char_p
+    L.libsortDebugSetPortionTiles.argtypes = [u32]
+    L.libsortDebugSetPortionTiles.restype = None
+    if hasattr(L, "libsortDeviceHistogram"):
+        L.libsortDeviceHistogram.argtypes = [vp, sz, u32, u32, vp, vp]
+        L.libsortDeviceHistogram.restype = ci
+    if hasattr(L, "libsortDeviceScatterToPeers"):
+        L.libsortDeviceScatterToPeers.argtypes = [vp, sz, u32, u32, vp, vp, vp, sz, vp]
+        L.libsortDeviceScatterToPeers.restype = ci
+    if hasattr(L, "libsortIpcExport"):
+        L.libsortIpcExport.argtypes = [vp, vp]
+        L.libsortIpcExport.restype = ci
+        L.libsortIpcOpen.argtypes = [vp, ctypes.POINTER(vp)]
+        L.libsortIpcOpen.restype = ci
+        L.libsortIpcClose.argtypes = [vp]
+        L.libsortIpcClose.restype = ci
+    _lib = L
+    return L
+
+
+_inited = False
+
+
+def init_once():
+    """initLibSort exactly once per process (reference libsort.go:22-33 guards the same way)."""
+    global _inited
+    if not _inited:
+        if not lib().initLibSort():
+            raise RuntimeError("initLibSort failed (no usable CUDA device?)")
+        _inited = True
+
+
+def check(code, what="libsort"):
+    if code != 0:
+        raise RuntimeError("%s failed: %s (%d)" % (what, lib().libsortErrorString(code).decode(), code))

@@ -1,0 +1,215 @@
+"""GPU parity: the CUDA path, called through the C ABI, against the oracle
+(bit-exact: keys and boundaries), the committed golden vectors of the reference
+GPU path and -- when oracle/_ref loads -- the reference itself run side by side."""
+import ctypes
+import glob
+import os
+import re
+import threading
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+
+SIZES = [1, 2, 127, 128, 129, 255, 1021, 1111, 4099, 8191, 8192, 8193, 100003, (1 << 20) + 5]
+COMBOS = [(0, 8), (4, 8), (0, 4), (8, 8), (16, 8), (24, 8), (0, 16), (16, 16), (0, 2), (30, 2), (6, 10)]
+
+
+def provided_gpu(lib, keys):
+    x = np.ascontiguousarray(keys, dtype=np.uint32).copy()
+    assert lib.providedGpu(x.ctypes.data, x.size) is True
+    return x
+
+
+def gpu_partial(lib, keys, off, w):
+    x = np.ascontiguousarray(keys, dtype=np.uint32).copy()
+    b = np.full(1 << w, 0xDEADBEEF, dtype=np.uint32)
+    assert lib.gpuPartial(x.ctypes.data, b.ctypes.data, x.size, off, w) is True
+    return x, b
+
+
+def skewed(oracle, n):
+    x = oracle.pcg_stream(n)
+    return {
+        "consthigh": (np.uint32(0xAB000000) | (x & np.uint32(0x00FFFFFF))).astype(np.uint32),
+        "consthigh16": (np.uint32(0xABCD0000) | (x & np.uint32(0xFFFF))).astype(np.uint32),
+        "zipf": (np.floor(2.0 ** (32.0 * x.astype(np.float64) / 2.0 ** 32)) - 1).astype(np.uint32),
+        "allequal": np.full(n, 0x12345678, dtype=np.uint32),
+        "allones": np.full(n, 0xFFFFFFFF, dtype=np.uint32),
+        "nogroup0": (x | np.uint32(0x01010101)).astype(np.uint32),
+        "nogroup1": (x & ~np.uint32(0x01010101)).astype(np.uint32),
+        "descending": np.arange(n, 0, -1, dtype=np.uint32),
+    }
+
+
+@pytest.mark.parametrize("n", SIZES)
+def test_provided_gpu_equals_oracle(gpu_lib, oracle, n):
+    k = oracle.pcg_stream(n)
+    assert np.array_equal(provided_gpu(gpu_lib, k), oracle.full_sort(k))
+
+
+def test_empty_input(gpu_lib):
+    x = np.empty(0, np.uint32)
+    assert gpu_lib.providedGpu(x.ctypes.data, 0) is True
+    b = np.full(256, 7, np.uint32)
+    assert gpu_lib.gpuPartial(x.ctypes.data, b.ctypes.data, 0, 0, 8) is True
+    assert not b.any()
+
+
+@pytest.mark.parametrize("n", [1, 129, 1021, 1111, 4099, 8193, 100003])
+@pytest.mark.parametrize("off,w", COMBOS)
+def test_gpu_partial_equals_oracle(gpu_lib, oracle, n, off, w):
+    k = oracle.pcg_stream(n)
+    got, gb = gpu_partial(gpu_lib, k, off, w)
+    want, wb = oracle.gpu_partial(k, off, w)
+    assert np.array_equal(got, want)
+    assert np.array_equal(gb, wb)
+
+
+@pytest.mark.parametrize("off,w", [(0, 8), (16, 8), (24, 8), (16, 16), (0, 16), (0, 4), (28, 4), (0, 2)])
+def test_skewed_inputs_reference_boundaries(gpu_lib, oracle, off, w):
+    """Empty leading groups: boundaries must reproduce the reference's
+    gpu_groups/back-fill output (sort.cu:14-27,381-387), not the prefix sums."""
+    for name, k in skewed(oracle, 5000).items():
+        got, gb = gpu_partial(gpu_lib, k, off, w)
+        want, wb = oracle.gpu_partial(k, off, w)
+        assert np.array_equal(got, want), name
+        assert np.array_equal(gb, wb), name
+        assert np.array_equal(provided_gpu(gpu_lib, k), np.sort(k)), name
+
+
+def test_exact_boundary_mode_device_api(gpu_lib, oracle, pkg):
+    import torch
+    dev = importlib_device(pkg)
+    for name, k in list(skewed(oracle, 30000).items()) + [("uniform", oracle.pcg_stream(30000))]:
+        t = torch.from_numpy(k.view(np.int32)).cuda()
+        for off, w in [(0, 8), (24, 8), (16, 16), (8, 12)]:
+            out, b = dev.sort_bits(t, off, w, boundaries=True, boundary_mode=pkg.binding.BOUNDS_EXACT)
+            assert np.array_equal(out.cpu().numpy().view(np.uint32), oracle.step(k, off, w)), name
+            assert np.array_equal(b.cpu().numpy().view(np.uint32), oracle.boundaries_exact(k, off, w)), name
+        assert np.array_equal(t.cpu().numpy().view(np.uint32), k)   # input untouched
+
+
+def importlib_device(pkg):
+    import importlib
+    return importlib.import_module(pkg.__name__ + ".device")
+
+
+def test_device_api_in_place_and_misaligned(gpu_lib, oracle, pkg):
+    import torch
+    dev = importlib_device(pkg)
+    k = oracle.pcg_stream(50001)
+    big = torch.from_numpy(k.view(np.int32)).cuda()
+    for off in (0, 1, 3):   # element offsets 1 and 3: pointer not 16 B aligned -> non-TMA path
+        t = big[off:].clone() if off == 0 else big[off:]
+        src = k[off:]
+        out = dev.sort(t.contiguous() if off == 0 else t)
+        assert np.array_equal(out.cpu().numpy().view(np.uint32), np.sort(src))
+    t = big.clone()
+    out = dev.sort_bits(t, 0, 8, out=t)      # in place with an odd pass count
+    assert np.array_equal(out.cpu().numpy().view(np.uint32), oracle.step(k, 0, 8))
+    t = big.clone()
+    out = dev.sort_bits(t, 0, 32, out=t)     # in place, even pass count
+    assert np.array_equal(out.cpu().numpy().view(np.uint32), np.sort(k))
+
+
+def test_lookback_portions(gpu_lib, oracle):
+    """Force several look-back portions (carry of bucket bases between launches)."""
+    tile = gpu_lib.libsortTileKeys()
+    k = oracle.pcg_stream(tile * 17 + 123)
+    gpu_lib.libsortDebugSetPortionTiles(3)
+    try:
+        assert np.array_equal(provided_gpu(gpu_lib, k), np.sort(k))
+        got, gb = gpu_partial(gpu_lib, k, 8, 16)
+        want, wb = oracle.gpu_partial(k, 8, 16)
+        assert np.array_equal(got, want) and np.array_equal(gb, wb)
+    finally:
+        gpu_lib.libsortDebugSetPortionTiles(0)
+
+
+def test_golden_reference_gpu_outputs(gpu_lib):
+    files = sorted(glob.glob(os.path.join(GOLDEN, "ref_*.npz")))
+    assert files, "golden fixtures missing"
+    for f in files:
+        z = np.load(f)
+        for name in sorted(k[:-5] for k in z.files if k.endswith("__out")):
+            keys = z["in__" + re.sub(r"^(full_|part_)|_o\d+_w\d+$", "", name)]
+            if name.startswith("full"):
+                assert np.array_equal(provided_gpu(gpu_lib, keys), z[name + "__out"]), name
+            else:
+                off, w = int(z[name + "__ow"][0]), int(z[name + "__ow"][1])
+                got, gb = gpu_partial(gpu_lib, keys, off, w)
+                assert np.array_equal(got, z[name + "__out"]), name
+                assert np.array_equal(gb, z[name + "__bounds"]), name
+
+
+def test_side_by_side_with_compiled_reference(gpu_lib, oracle):
+    """The unmodified reference (oracle/_ref, sm_100a build) on the same GPU."""
+    if not oracle.ref_available():
+        pytest.skip("oracle/_ref not present")
+    r = oracle.ref()
+    if not getattr(test_side_by_side_with_compiled_reference, "_inited", False):
+        assert r.initLibSort()
+        test_side_by_side_with_compiled_reference._inited = True
+    u32p = ctypes.POINTER(ctypes.c_uint32)
+    cases = [("uniform", oracle.pcg_stream(200000))] + list(skewed(oracle, 20000).items())
+    for name, k in cases:
+        a = k.copy()
+        assert r.providedGpu(a.ctypes.data_as(u32p), a.size)
+        assert np.array_equal(provided_gpu(gpu_lib, k), a), name
+        for off, w in [(0, 8), (8, 8), (24, 8), (0, 16), (16, 16), (4, 8)]:
+            a = k.copy()
+            rb = np.zeros(1 << w, np.uint32)
+            assert r.gpuPartial(a.ctypes.data_as(u32p), rb.ctypes.data_as(u32p), a.size, off, w)
+            got, gb = gpu_partial(gpu_lib, k, off, w)
+            assert np.array_equal(got, a), (name, off, w)
+            assert np.array_equal(gb, rb), (name, off, w)
+
+
+def test_concurrent_callers(gpu_lib, oracle):
+    """16 host threads at once, full and partial, as in the reference's
+    TestParallel (benchmark/pkg/sort/libsort_test.go:35-87)."""
+    k = oracle.pcg_stream(4099)
+    want_full, (want_part, want_b) = np.sort(k), oracle.gpu_partial(k, 0, 8)
+    errs = []
+
+    def worker(i):
+        try:
+            if i % 2:
+                assert np.array_equal(provided_gpu(gpu_lib, k), want_full)
+            else:
+                got, gb = gpu_partial(gpu_lib, k, 0, 8)
+                assert np.array_equal(got, want_part) and np.array_equal(gb, want_b)
+        except Exception as e:  # noqa: BLE001
+            errs.append(repr(e))
+
+    th = [threading.Thread(target=worker, args=(i,)) for i in range(16)]
+    [t.start() for t in th]
+    [t.join(30) for t in th]
+    assert not errs and not any(t.is_alive() for t in th)
+
+
+def test_second_init_fails_and_oversize_rejected(gpu_lib):
+    assert gpu_lib.initLibSort() is False                      # utils.cu:14-17
+    x = np.zeros(4, np.uint32)
+    assert gpu_lib.providedGpu(x.ctypes.data, (1 << 32) + 5) is False   # invokers.cu:54-57
+
+
+def test_pylibsort_wrapper(gpu_lib, oracle, pkg):
+    """Mirror of faasTest/testPyLibSort.py:195-245 (testSortFull / testSortPartial)."""
+    import importlib
+    pls = importlib.import_module(pkg.__name__ + ".pylibsort")
+    k = oracle.pcg_stream(1021)
+    buf = bytearray(k.tobytes())
+    pls.sortFull(buf)
+    pls.checkSortFull(pls.bytesToInts(buf), k)
+    pls.checkOrder(pls.bytesToInts(buf))
+    buf = bytearray(k.tobytes())
+    bounds = pls.sortPartial(buf, 4, 8)
+    want, wb = oracle.gpu_partial(k, 4, 8)
+    assert np.array_equal(pls.bytesToInts(buf), want) and bounds == wb.tolist()
+    caps = np.diff(np.array(bounds, dtype=np.int64) * 4, append=len(buf))    # data.py:301-304
+    pls.checkPartial(k.tobytes(), buf, caps, 4, 8)
+    assert len(pls.generateInputs(10)) == 40
