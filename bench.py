@@ -1,0 +1,348 @@
+#!/usr/bin/env python3
+"""bench.py -- headline benchmark of the B200-native libsort.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+N = 1: BASELINE.json configs[1] -- full LSD sort of 2^28 uniform uint32 keys
+       (first 2^28 outputs of the library's PCG stream) on one B200.
+N > 1: the distributed sort (configs[3] shape, weak scaling): 2^28 keys per GPU,
+       one rank per GPU under torchrun, MSD bucketing -> count all-gather ->
+       key exchange over NVLink -> local LSD sort.
+
+One JSON line on stdout (rank 0).  `value` is device-resident whole-job
+Gkeys/s; `e2e` is the same sort through the reference-facing C ABI
+(providedGpu, host buffers, H2D + D2H inside the timed region).
+`--impl reference` times the reference's own CPU implementation of the path
+(providedCpu = single-threaded std::sort, libsort/invokers.cu:68-71) from
+oracle/_ref (or the oracle port) on a bounded sample of the same workload.
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_PER_GPU = 1 << 28
+METRIC = "Gkeys/s uint32 sort"
+UNIT = "Gkeys/s"
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:  # noqa: BLE001
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except Exception:  # noqa: BLE001
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.t.join(2)
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            p = [x.strip() for x in ln.split(",")]
+            if len(p) < 7:
+                continue
+            try:
+                sm.append(float(p[0]))
+                mx = float(p[1])
+            except ValueError:
+                continue
+            for nm, v in zip(names, p[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+def cpu_reference_sorter():
+    """(callable(np.uint32 array) -> None in place, kind)"""
+    from oracle import oracle as o
+    import ctypes
+    if o.ref_available():
+        try:
+            r = o.ref()
+            u32p = ctypes.POINTER(ctypes.c_uint32)
+            return (lambda a: r.providedCpu(a.ctypes.data_as(u32p), a.size)), "reference"
+        except OSError:
+            pass
+    L = o.lib()
+    u32p = ctypes.POINTER(ctypes.c_uint32)
+    return (lambda a: L.oracle_cpu_sort(a.ctypes.data_as(u32p), a.size)), "port"
+
+
+def pcg_keys(n):
+    """First n outputs of populateInput in a fresh process."""
+    import numpy as np
+    pkg = importlib.import_module("gpu-radix-sort_b200")
+    a = np.empty(n, dtype=np.uint32)
+    pkg.lib().populateInput(a.ctypes.data, n)
+    return a
+
+
+def time_cpu(sample_keys, reps):
+    import numpy as np
+    sorter, kind = cpu_reference_sorter()
+    best = []
+    for _ in range(reps):
+        a = sample_keys.copy()
+        t0 = time.perf_counter()
+        sorter(a)
+        best.append(time.perf_counter() - t0)
+    assert bool(np.all(a[1:] >= a[:-1]))
+    return sum(best) / len(best), kind
+
+
+def run_reference(args, rank, world):
+    """The reference's CPU path on the host cores; rank 0 only."""
+    if rank != 0:
+        return
+    import numpy as np
+    sample_n = 1 << 24   # bounded sample of the 2^28-key workload: ~1.5 s of std::sort per step
+    keys = np.empty(sample_n, dtype=np.uint32)
+    from oracle import oracle as o
+    keys[:] = o.pcg_stream(sample_n)
+    sorter, kind = cpu_reference_sorter()
+    for _ in range(min(args.warmup, 1)):
+        sorter(keys.copy())
+    t = 0.0
+    for _ in range(args.steps):
+        a = keys.copy()
+        t0 = time.perf_counter()
+        sorter(a)
+        t += time.perf_counter() - t0
+    val = sample_n * args.steps / t / 1e9
+    sample = "first 2^24 keys of the PCG stream per step (of the 2^28-key workload), std::sort, 1 thread"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": t / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+        "config": {"workload": "256M uniform uint32 full sort (BASELINE configs[1])", "sample_keys": sample_n},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": 1, "kind": kind, "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_single(args):
+    import numpy as np
+    import torch
+    pkg = importlib.import_module("gpu-radix-sort_b200")
+    dev = importlib.import_module("gpu-radix-sort_b200.device")
+    binding = pkg.binding
+    binding.init_once()
+    torch.cuda.set_device(0)
+    n = args.keys
+    h_keys = pcg_keys(n)
+    d_in = torch.from_numpy(h_keys.view(np.int32)).cuda()
+    d_out, d_tmp = torch.empty_like(d_in), torch.empty_like(d_in)
+
+    for _ in range(max(args.warmup, 3)):
+        dev.sort(d_in, out=d_out, tmp=d_tmp)
+    torch.cuda.synchronize()
+    clocks = ClockSampler(0)
+    clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(args.steps):
+        dev.sort(d_in, out=d_out, tmp=d_tmp)   # input (1 GiB) is pristine every step and larger than L2
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / args.steps
+    clk = clocks.stop()
+
+    # sortedness + multiset check of the last timed result (size-independent properties)
+    out_u = d_out.view(torch.uint8).view(-1, 4)  # avoid signed compare: check via int64
+    o64 = d_out.to(torch.int64) & 0xFFFFFFFF
+    assert bool((o64[1:] >= o64[:-1]).all()), "device sort output not ascending"
+    i64 = d_in.to(torch.int64) & 0xFFFFFFFF
+    assert int(o64.sum()) == int(i64.sum()) and int((o64 * o64 % 1000003).sum()) == int((i64 * i64 % 1000003).sum())
+    del o64, i64, out_u
+
+    # per-kernel durations, CUDA events on the launching stream (live, same process)
+    kt_acc, reps = None, 5
+    for _ in range(reps):
+        kt = binding.KernelTimes()
+        dev.sort(d_in, out=d_out, tmp=d_tmp, times=kt)
+        vals = [kt.memset_ms, kt.histogram_ms, kt.scan_ms] + [kt.pass_ms[i] for i in range(kt.npass)]
+        kt_acc = vals if kt_acc is None else [a + b for a, b in zip(kt_acc, vals)]
+    kt_avg = [v / reps for v in kt_acc]
+    pass_ms = sum(kt_avg[3:]) / len(kt_avg[3:])
+    peak, peak_src = measured_peak()
+    achieved = 8.0 * n / (pass_ms * 1e-3) / 1e9
+    traffic = None
+    tfile = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tfile):
+        try:
+            traffic = json.load(open(tfile)).get("k_onesweep_dram_bytes_per_launch")
+        except Exception:  # noqa: BLE001
+            traffic = None
+
+    # e2e: reference-facing C ABI, pinned host buffers, copies inside the timed region
+    lib = pkg.lib()
+    h_src = torch.from_numpy(h_keys.view(np.int32)).pin_memory()
+    h_work = torch.empty_like(h_src).pin_memory()
+    e2e_steps = max(1, min(args.steps, 5))
+    for _ in range(2):
+        h_work.copy_(h_src)
+        assert lib.providedGpu(h_work.data_ptr(), n)
+    t_e2e = 0.0
+    for _ in range(e2e_steps):
+        h_work.copy_(h_src)
+        t0 = time.perf_counter()
+        ok = lib.providedGpu(h_work.data_ptr(), n)
+        t_e2e += time.perf_counter() - t0
+        assert ok
+    hw = h_work.numpy().view(np.uint32)
+    assert bool(np.all(hw[1:] >= hw[:-1]))
+    e2e_val = n * e2e_steps / t_e2e / 1e9
+
+    cpu_n = 1 << 26
+    cpu_s, cpu_kind = time_cpu(h_keys[:cpu_n], 3)
+    line = {
+        "metric": METRIC, "value": n / (ms * 1e-3) / 1e9, "unit": UNIT, "n_gpus": 1, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+        "config": {"workload": "256M uniform uint32 full LSD sort, 8-bit digits, 4 passes (BASELINE configs[1])",
+                   "keys": n, "input": "first n outputs of populateInput (PCG32)", "tile_keys": lib.libsortTileKeys(),
+                   "l2": "input 1 GiB per step, larger than the 126 MB L2; not flushed between steps"},
+        "clocks": clk,
+        "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": 4 * n, "d2h_bytes_per_step": 4 * n,
+                "ms_per_step": t_e2e / e2e_steps * 1e3, "steps": e2e_steps, "api": "providedGpu (host pointers, pinned)"},
+        "gpu_launches": 6 * args.steps,
+        "roofline": {"bound": "hbm", "kernel": "k_onesweep (one 8-bit scatter pass)", "achieved": achieved,
+                     "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                     "algorithmic_bytes_per_launch": 8 * n, "avg_launch_ms": pass_ms},
+        "kernels_ms": {"memset": kt_avg[0], "k_histogram": kt_avg[1], "k_scan_hist": kt_avg[2],
+                       "k_onesweep": kt_avg[3:]},
+        "whole_sort_roofline": {"algorithmic_bytes": 36 * n, "achieved": 36.0 * n / (ms * 1e-3) / 1e9,
+                                "frac": 36.0 * n / (ms * 1e-3) / 1e9 / peak},
+        "cpu_baseline": {"value": cpu_n / cpu_s / 1e9, "unit": UNIT, "cores": 1, "kind": cpu_kind,
+                         "sample": "first 2^26 keys of the same PCG stream, mean of 3 std::sort runs (%.2f s each)" % cpu_s},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_multi(args, rank, world, local_rank):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    pkg = importlib.import_module("gpu-radix-sort_b200")
+    distrib = importlib.import_module("gpu-radix-sort_b200.distrib")
+    torch.cuda.set_device(local_rank)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    n = args.keys
+    # one continuous PCG stream; rank g owns elements [g*n, (g+1)*n)  
+    from oracle import oracle as o   # input generation only (jump-ahead of the stream); never timed
+    d_in = distrib.shard_of_pcg_stream(rank, n)
+    sorter = distrib.DistributedSorter(n, dist.group.WORLD, mode=args.exchange)
+    for _ in range(max(args.warmup, 3)):
+        sorter.sort(d_in)
+    torch.cuda.synchronize()
+    dist.barrier()
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        out, cnt = sorter.sort(d_in)
+    e1.record()
+    torch.cuda.synchronize()
+    dist.barrier()
+    ms_local = torch.tensor([e0.elapsed_time(e1) / args.steps], device="cuda")
+    dist.all_reduce(ms_local, op=dist.ReduceOp.MAX)
+    ms = float(ms_local.item())
+    clk = clocks.stop()
+    stats = sorter.verify(d_in, out, cnt)           # sortedness, rank ordering, multiset fingerprint
+    phases = sorter.phase_times(d_in)               # per-phase CUDA-event times, max over ranks
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        total = n * world
+        exch_bytes = 4.0 * n * (world - 1) / world
+        line = {
+            "metric": METRIC, "value": total / (ms * 1e-3) / 1e9, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+            "config": {"workload": "distributed uint32 sort, 2^28 keys per GPU (BASELINE configs[3] shape)",
+                       "keys_per_gpu": n, "keys_total": total, "exchange": args.exchange,
+                       "parallelism": "key-range sharding, 1 rank/GPU, MSD bucketing + exchange + local LSD",
+                       "l2": "1 GiB shard per step per GPU, larger than L2"},
+            "clocks": clk, "verify": stats, "phases_ms": phases,
+            "gpu_launches": sorter.launches_per_sort * args.steps,
+            "roofline": {"bound": "hbm", "kernel": "k_onesweep (local sort pass)", "achieved": phases.get("pass_gbs"),
+                         "peak": peak, "peak_source": peak_src, "unit": "GB/s",
+                         "frac": (phases.get("pass_gbs") or 0) / peak, "traffic": None},
+            "nvlink": {"bytes_out_per_gpu": exch_bytes, "exchange_ms": phases.get("exchange_ms"),
+                       "gbs_per_direction": exch_bytes / (phases["exchange_ms"] * 1e-3) / 1e9 if phases.get("exchange_ms") else None,
+                       "peak_gbs": 770.0, "peak_source": "measured peer copy per direction (B200_PROFILING.md)"},
+            "e2e": sorter.e2e(args, d_in),
+        }
+        print(json.dumps(line), flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--keys", type=int, default=N_PER_GPU, help="keys per GPU")
+    ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
+                    help="multi-GPU key exchange: fused scatter into peer memory, or NCCL all-to-all")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if world == 1 and args.gpus == 1:
+        run_single(args)
+    elif world == 1:
+        raise SystemExit("for --gpus N > 1 launch with: python -m torch.distributed.run --nnodes=1 "
+                         "--nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...")
+    else:
+        run_multi(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

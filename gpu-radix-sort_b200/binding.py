@@ -11,8 +11,8 @@ LEGACY_SYMBOLS = ["initLibSort", "gpuPartial", "providedGpu", "providedCpu", "po
                   "gpuPartialProfile", "providedGpuProfile"]
 ADDITIVE_SYMBOLS = ["libsortTileKeys", "libsortWorkspaceBytes", "libsortDeviceSort", "libsortDeviceCount",
                     "libsortReleaseCaches", "libsortErrorString", "libsortDebugSetPortionTiles",
-                    "libsortDeviceHistogram", "libsortDeviceScatterToPeers", "libsortIpcExport", "libsortIpcOpen",
-                    "libsortIpcClose"]
+                    "libsortDeviceSample", "libsortDevicePickSplitters", "libsortDeviceSplitCounts", "libsortPopulateInputAt", "libsortDeviceScatterToPeers",
+                    "libsortIpcAlloc", "libsortIpcFree", "libsortIpcExport", "libsortIpcOpen", "libsortIpcClose"]
 
 BOUNDS_REFERENCE = 0
 BOUNDS_EXACT = 1
@@ -77,19 +77,21 @@ def lib():
     L.libsortErrorString.restype = ctypes.c_char_p
     L.libsortDebugSetPortionTiles.argtypes = [u32]
     L.libsortDebugSetPortionTiles.restype = None
-    if hasattr(L, "libsortDeviceHistogram"):
-        L.libsortDeviceHistogram.argtypes = [vp, sz, u32, u32, vp, vp]
-        L.libsortDeviceHistogram.restype = ci
-    if hasattr(L, "libsortDeviceScatterToPeers"):
-        L.libsortDeviceScatterToPeers.argtypes = [vp, sz, u32, u32, vp, vp, vp, sz, vp]
-        L.libsortDeviceScatterToPeers.restype = ci
-    if hasattr(L, "libsortIpcExport"):
-        L.libsortIpcExport.argtypes = [vp, vp]
-        L.libsortIpcExport.restype = ci
-        L.libsortIpcOpen.argtypes = [vp, ctypes.POINTER(vp)]
-        L.libsortIpcOpen.restype = ci
-        L.libsortIpcClose.argtypes = [vp]
-        L.libsortIpcClose.restype = ci
+    L.libsortDeviceSample.argtypes = [vp, sz, vp, u32, u32, vp]
+    L.libsortDevicePickSplitters.argtypes = [vp, sz, ci, vp, vp]
+    L.libsortDevicePickSplitters.restype = ci
+    L.libsortPopulateInputAt.argtypes = [vp, sz, ctypes.c_uint64]
+    L.libsortPopulateInputAt.restype = None
+    L.libsortDeviceSplitCounts.argtypes = [vp, sz, vp, ci, vp, vp]
+    L.libsortDeviceScatterToPeers.argtypes = [vp, sz, vp, ci, vp, vp, sz, vp]
+    L.libsortIpcAlloc.argtypes = [sz, ctypes.POINTER(vp)]
+    L.libsortIpcFree.argtypes = [vp]
+    L.libsortIpcExport.argtypes = [vp, vp]
+    L.libsortIpcOpen.argtypes = [vp, ctypes.POINTER(vp)]
+    L.libsortIpcClose.argtypes = [vp]
+    for name in ("libsortDeviceSample", "libsortDevicePickSplitters", "libsortDeviceSplitCounts", "libsortPopulateInputAt", "libsortDeviceScatterToPeers", "libsortIpcAlloc",
+                 "libsortIpcFree", "libsortIpcExport", "libsortIpcOpen", "libsortIpcClose"):
+        getattr(L, name).restype = ci
     _lib = L
     return L
 

@@ -324,3 +324,71 @@ API const char *libsortErrorString(int code)
 }
 
 API void libsortDebugSetPortionTiles(uint32_t tiles) { debug_set_portion_tiles(tiles); }
+
+// ---- distributed-sort building blocks (include/libsort_b200.h) ----------------
+
+API int libsortDeviceSample(const uint32_t *d_in, size_t n, uint32_t *d_out, uint32_t nsamples, uint32_t seed,
+                            void *stream)
+{
+    return (int)sample_keys(d_in, n, d_out, nsamples, seed, (cudaStream_t)stream);
+}
+
+API int libsortDevicePickSplitters(const uint32_t *d_sorted, size_t nsorted, int nranks, uint32_t *d_splitters,
+                                   void *stream)
+{
+    return (int)pick_splitters(d_sorted, nsorted, nranks, d_splitters, (cudaStream_t)stream);
+}
+
+// populateInput with an explicit position in the (fresh-process) stream:
+// arr[i] = element (first + i) of the PCG sequence of libsort/utils.cu:63-79.
+// Lets every rank generate its own shard of one continuous stream.
+API void libsortPopulateInputAt(uint32_t *arr, size_t nelem, uint64_t first)
+{
+    const uint64_t a = 6364136223846793005ull, c = 1442695040888963407ull;
+    uint64_t acc_mult = 1, acc_plus = 0, cur_mult = a, cur_plus = c, delta = first;
+    while (delta) {  // LCG jump-ahead (Brown, "Random number generation with arbitrary strides")
+        if (delta & 1) { acc_mult *= cur_mult; acc_plus = acc_plus * cur_mult + cur_plus; }
+        cur_plus = (cur_mult + 1) * cur_plus;
+        cur_mult *= cur_mult;
+        delta >>= 1;
+    }
+    uint64_t s = acc_mult * 0x4d595df4d0f33173ull + acc_plus;
+    for (size_t i = 0; i < nelem; i++) {
+        const uint64_t old = s;
+        s = old * a + c;
+        const uint32_t xorshifted = (uint32_t)((old ^ (old >> 18)) >> 27);
+        const uint32_t rot = (uint32_t)(old >> 59);
+        arr[i] = (xorshifted >> rot) | (xorshifted << ((0u - rot) & 31u));
+    }
+}
+
+API int libsortDeviceSplitCounts(const uint32_t *d_in, size_t n, const uint32_t *splitters, int nsplit,
+                                 uint32_t *d_counts, void *stream)
+{
+    return (int)split_counts(d_in, n, splitters, nsplit, d_counts, (cudaStream_t)stream);
+}
+
+API int libsortDeviceScatterToPeers(const uint32_t *d_in, size_t n, const uint32_t *splitters, int nsplit,
+                                    const unsigned long long *dest_ptrs, void *d_workspace, size_t workspace_len,
+                                    void *stream)
+{
+    return (int)scatter_by_splitters(d_in, n, splitters, nsplit, dest_ptrs, d_workspace, workspace_len,
+                                     (cudaStream_t)stream);
+}
+
+// Peer-mappable device memory for the exchange: plain cudaMalloc (one
+// allocation per handle, so cudaIpc maps it at offset 0).
+API int libsortIpcAlloc(size_t bytes, void **ptr) { return (int)cudaMalloc(ptr, bytes); }
+API int libsortIpcFree(void *ptr) { return (int)cudaFree(ptr); }
+API int libsortIpcExport(void *ptr, void *handle64)
+{
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+    return (int)cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t *>(handle64), ptr);
+}
+API int libsortIpcOpen(const void *handle64, void **ptr)
+{
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, sizeof(h));
+    return (int)cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess);
+}
+API int libsortIpcClose(void *ptr) { return (int)cudaIpcCloseMemHandle(ptr); }

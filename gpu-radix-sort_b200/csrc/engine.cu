@@ -116,10 +116,13 @@ static cudaError_t dev_info(DevInfo **out)
     if (!d.ready) {
         e = cudaDeviceGetAttribute(&d.sms, cudaDevAttrMultiProcessorCount, dev);
         if (e != cudaSuccess) return e;
-        auto kern = k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, 8>;
+        auto kern = k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, 8, RadixBinner, false>;
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem));
         if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, 0>,
+        e = cudaFuncSetAttribute(k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, 0, RadixBinner, false>,
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem));
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, 0, SplitBinner, true>,
                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem));
         if (e != cudaSuccess) return e;
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.sort_occ, kern, SORT_THREADS, sizeof(SortSmem));
@@ -281,10 +284,10 @@ cudaError_t sort_bits(const uint32_t *in, uint32_t *a, uint32_t *b, uint32_t *wa
             const int grid = (int)std::min<size_t>(nt, (size_t)dev->sms * dev->sort_occ);
             uint32_t *bcur = base + ((q & 1) * MAX_PASSES + p) * RADIX;
             uint32_t *bnext = (q + 1 < nportions) ? base + (((q + 1) & 1) * MAX_PASSES + p) * RADIX : nullptr;
-            auto kern = plan.mask[p] == 0xffu ? k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, 8>
-                                              : k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, 0>;
+            auto kern = plan.mask[p] == 0xffu ? k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, 8, RadixBinner, false>
+                                              : k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, 0, RadixBinner, false>;
             kern<<<grid, SORT_THREADS, sizeof(SortSmem), st>>>(
-                src + k0, dst, (uint32_t)(k1 - k0), plan.shift[p], plan.mask[p], bcur, bnext,
+                src + k0, dst, (uint32_t)(k1 - k0), RadixBinner::Arg{plan.shift[p], plan.mask[p]}, bcur, bnext,
                 desc + ((size_t)p * ntiles + t0) * RADIX, tickets + p * MAX_PORTIONS + q, nt, use_tma);
             launches++;
         }
@@ -322,6 +325,59 @@ cudaError_t sort_bits(const uint32_t *in, uint32_t *a, uint32_t *b, uint32_t *wa
         times->launches = launches;
     }
     return cudaSuccess;
+}
+
+// ---- distributed-sort building blocks ---------------------------------------
+cudaError_t sample_keys(const uint32_t *in, size_t n, uint32_t *out, uint32_t nsamples, uint32_t seed, cudaStream_t st)
+{
+    if (n == 0 || n > 0xffffffffull || nsamples == 0) return cudaErrorInvalidValue;
+    k_sample<<<(nsamples + 255) / 256, 256, 0, st>>>(in, (uint32_t)n, out, nsamples, seed);
+    return cudaGetLastError();
+}
+
+cudaError_t pick_splitters(const uint32_t *sorted, size_t nsorted, int nranks, uint32_t *d_splitters, cudaStream_t st)
+{
+    if (nranks < 1 || nranks > MAX_SPLITTERS + 1 || nsorted == 0 || nsorted > 0xffffffffull) return cudaErrorInvalidValue;
+    k_pick_splitters<<<1, 32, 0, st>>>(sorted, (uint32_t)nsorted, nranks, d_splitters);
+    return cudaGetLastError();
+}
+
+cudaError_t split_counts(const uint32_t *in, size_t n, const uint32_t *splitters, int nsplit, uint32_t *d_counts,
+                         cudaStream_t st)
+{
+    if (nsplit < 0 || nsplit > MAX_SPLITTERS) return cudaErrorInvalidValue;
+    DevInfo *dev = nullptr;
+    CK(dev_info(&dev));
+    CK(cudaMemsetAsync(d_counts, 0, (MAX_SPLITTERS + 1) * sizeof(uint32_t), st));
+    if (n == 0) return cudaSuccess;
+    const size_t want = (n / 4 + 4095) / 4096;
+    const int grid = (int)std::max<size_t>(1, std::min<size_t>((size_t)dev->sms * 2, want));
+    k_dest_hist<<<grid, 1024, 0, st>>>(in, n, SplitBinner::Arg{splitters, nsplit}, d_counts);
+    return cudaGetLastError();
+}
+
+cudaError_t scatter_by_splitters(const uint32_t *in, size_t n, const uint32_t *splitters, int nsplit,
+                                 const unsigned long long *dest_ptrs, void *workspace, size_t workspace_len,
+                                 cudaStream_t st)
+{
+    if (nsplit < 0 || nsplit > MAX_SPLITTERS || n >= (1ull << 30)) return cudaErrorInvalidValue;
+    if (n == 0) return cudaSuccess;
+    if (workspace_len < workspace_bytes(n) || !workspace) return cudaErrorInvalidValue;
+    DevInfo *dev = nullptr;
+    CK(dev_info(&dev));
+    uint32_t *ws = static_cast<uint32_t *>(workspace);
+    const size_t ntiles = num_tiles(n);
+    CK(cudaMemsetAsync(ws, 0, (WS_DESC + ntiles * RADIX) * sizeof(uint32_t), st));
+    PtrTable t{};
+    for (int i = 0; i <= nsplit; i++) t.p[i] = dest_ptrs[i];
+    unsigned long long *d_ptrs = reinterpret_cast<unsigned long long *>(ws + WS_HIST);
+    k_store_ptrs<<<1, 32, 0, st>>>(t, d_ptrs);
+    const int grid = (int)std::min<size_t>(ntiles, (size_t)dev->sms * dev->sort_occ);
+    const int use_tma = (reinterpret_cast<uintptr_t>(in) & 15u) == 0;
+    k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, 0, SplitBinner, true><<<grid, SORT_THREADS, sizeof(SortSmem), st>>>(
+        in, nullptr, (uint32_t)n, SplitBinner::Arg{splitters, nsplit}, d_ptrs, nullptr, ws + WS_DESC, ws + WS_TICKET,
+        (uint32_t)ntiles, use_tma);
+    return cudaGetLastError();
 }
 
 }  // namespace b200sort

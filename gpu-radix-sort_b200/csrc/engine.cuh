@@ -42,6 +42,22 @@ cudaError_t sort_bits(const uint32_t *in, uint32_t *a, uint32_t *b, uint32_t *wa
                       uint32_t width, uint32_t *d_bounds, int bounds_mode, void *workspace, size_t workspace_len,
                       cudaStream_t stream, uint32_t **result, KernelTimes *times);
 
+// Distributed-sort building blocks (one rank per GPU).
+// sample_keys: nsamples stratified pseudo-random keys of the shard.
+// pick_splitters: d_splitters[g-1] = g/nranks quantile of the sorted sample.
+// split_counts: d_counts[0..nsplit] = keys per destination, destination of a
+//   key = number of splitters <= key (DEVICE array, ascending, nsplit <= 15).
+// scatter_by_splitters: stable partition of the shard by destination, written
+//   straight to dest_ptrs[d] (device pointers, local or NVLink-mapped peer
+//   memory) -- the fused partition + key exchange; n < 2^30.
+cudaError_t sample_keys(const uint32_t *in, size_t n, uint32_t *out, uint32_t nsamples, uint32_t seed, cudaStream_t st);
+cudaError_t pick_splitters(const uint32_t *sorted, size_t nsorted, int nranks, uint32_t *d_splitters, cudaStream_t st);
+cudaError_t split_counts(const uint32_t *in, size_t n, const uint32_t *splitters, int nsplit, uint32_t *d_counts,
+                         cudaStream_t st);
+cudaError_t scatter_by_splitters(const uint32_t *in, size_t n, const uint32_t *splitters, int nsplit,
+                                 const unsigned long long *dest_ptrs, void *workspace, size_t workspace_len,
+                                 cudaStream_t st);
+
 // Test hook: cap the number of tiles per look-back portion (0 = default,
 // i.e. the largest portion whose key count fits the 30-bit descriptors).
 void debug_set_portion_tiles(uint32_t tiles);

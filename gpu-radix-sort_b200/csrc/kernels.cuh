@@ -235,6 +235,38 @@ __device__ __forceinline__ uint32_t leader_atom_add(uint32_t smem_addr, uint32_t
     return old;
 }
 
+// Which bin a key falls into.  RadixBinner: an (up to) 8-bit digit, the LSD/MSD
+// pass.  SplitBinner: destination rank of the distributed sort = number of
+// splitters <= key (splitters ascending, at most 15 -> up to 16 ranks).
+struct RadixBinner {
+    struct Arg { uint32_t shift, mask; };
+    uint32_t shift, mask;
+    __device__ __forceinline__ explicit RadixBinner(const Arg &a) : shift(a.shift), mask(a.mask) {}
+    __device__ __forceinline__ uint32_t bin(uint32_t key) const { return (key >> shift) & mask; }
+    __device__ __forceinline__ uint32_t pad_bin() const { return mask; }  // bin of the 0xffffffff padding keys
+    __device__ __forceinline__ int nbits() const { return __popc(mask); }
+};
+constexpr int MAX_SPLITTERS = 15;
+struct SplitBinner {
+    struct Arg { const uint32_t *d_splitters; int nsplit; };  // splitters live in device memory (no host round trip)
+    uint32_t v[MAX_SPLITTERS];
+    int nsplit;
+    __device__ __forceinline__ explicit SplitBinner(const Arg &a) : nsplit(a.nsplit)
+    {
+#pragma unroll
+        for (int j = 0; j < MAX_SPLITTERS; j++) v[j] = j < a.nsplit ? a.d_splitters[j] : 0xffffffffu;
+    }
+    __device__ __forceinline__ uint32_t bin(uint32_t key) const
+    {
+        uint32_t d = 0;
+#pragma unroll
+        for (int j = 0; j < MAX_SPLITTERS; j++) d += (j < nsplit && key >= v[j]) ? 1u : 0u;
+        return d;
+    }
+    __device__ __forceinline__ uint32_t pad_bin() const { return (uint32_t)nsplit; }
+    __device__ __forceinline__ int nbits() const { return 32 - __clz(nsplit); }  // bins 0..nsplit
+};
+
 template <int THREADS, int KPT>
 struct OnesweepSmem {
     static constexpr int TILE = THREADS * KPT;
@@ -242,6 +274,7 @@ struct OnesweepSmem {
     alignas(128) uint32_t keys[2][TILE];       // TMA destinations, re-used for the sorted tile
     uint32_t warp_hist[NWARPS][RADIX];         // per-warp digit counters -> running offsets
     uint32_t tile_offs[RADIX];                 // global dst of bucket b minus its start in the tile
+    unsigned long long tile_ptr[RADIX];        // PTR_OUT: byte address of the same, possibly in peer memory
     uint32_t s_warp[8];
     alignas(8) uint64_t mbar[2];
     uint32_t next_tile[2];
@@ -251,10 +284,12 @@ struct OnesweepSmem {
 // descriptor value).  base: global bucket bases for this portion;
 // base_next (nullable): receives base + portion bucket totals for the next
 // portion.  desc: ntiles x 256 zero-initialised descriptors; ticket: zeroed.
-template <int THREADS, int KPT, int MINB, int NBITS>
+// PTR_OUT: `base` holds one 64-bit destination pointer per bin (local or
+// NVLink-mapped peer memory) instead of an offset into `out`.
+template <int THREADS, int KPT, int MINB, int NBITS, class Binner, bool PTR_OUT>
 __global__ void __launch_bounds__(THREADS, MINB)
-    k_onesweep(const uint32_t *__restrict__ in, uint32_t *__restrict__ out, uint32_t n, uint32_t shift, uint32_t mask,
-               const uint32_t *__restrict__ base, uint32_t *__restrict__ base_next, uint32_t *__restrict__ desc,
+    k_onesweep(const uint32_t *__restrict__ in, uint32_t *__restrict__ out, uint32_t n, const typename Binner::Arg binner_arg,
+               const void *__restrict__ base_v, uint32_t *__restrict__ base_next, uint32_t *__restrict__ desc,
                uint32_t *__restrict__ ticket, uint32_t ntiles, int use_tma)
 {
     using Smem = OnesweepSmem<THREADS, KPT>;
@@ -266,7 +301,9 @@ __global__ void __launch_bounds__(THREADS, MINB)
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t lt = lanemask_lt();
-    const int nbits = __popc(mask);
+    const Binner binner(binner_arg);
+    const int nbits = binner.nbits();
+    const uint32_t pad_bin = binner.pad_bin();
 
     auto issue_load = [&](uint32_t tile, int buf) {
         // elected thread: arm the barrier and start the bulk copy of the
@@ -337,7 +374,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
 
         // (3) early counts: per-warp digit histogram
 #pragma unroll
-        for (int i = 0; i < KPT; i++) atomicAdd(&s.warp_hist[warp][digit_of(key[i], shift, mask)], 1u);
+        for (int i = 0; i < KPT; i++) atomicAdd(&s.warp_hist[warp][binner.bin(key[i])], 1u);
         __syncthreads();
 
         // (4) bin threads: reduce over warps, publish the tile aggregate,
@@ -347,7 +384,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
 #pragma unroll
             for (int w = 0; w < NWARPS; w++) my_count += s.warp_hist[w][tid];
             uint32_t agg = my_count;
-            if ((uint32_t)tid == mask) agg -= (uint32_t)TILE - valid;  // padding keys carry the top digit
+            if ((uint32_t)tid == pad_bin) agg -= (uint32_t)TILE - valid;  // padding keys carry the top digit
             st_relaxed(&desc[(size_t)cur * RADIX + tid], (cur == 0 ? DESC_INCL : DESC_AGG) | agg);
             my_count = agg | 0u;  // keep the unpadded count for the look-back
         }
@@ -355,7 +392,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
             uint32_t padded = 0;
             if (tid < RADIX) {
                 padded = my_count;
-                if ((uint32_t)tid == mask) padded += (uint32_t)TILE - valid;
+                if ((uint32_t)tid == pad_bin) padded += (uint32_t)TILE - valid;
             }
             my_start = block_excl_scan_256(padded, s.s_warp, nullptr);
         }
@@ -375,7 +412,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
         const uint32_t my_hist = smem_u32(&s.warp_hist[warp][0]);
 #pragma unroll
         for (int i = 0; i < KPT; i++) {
-            const uint32_t d = digit_of(key[i], shift, mask);
+            const uint32_t d = binner.bin(key[i]);
             const uint32_t peers = match_digit<NBITS>(d, nbits);
             const uint32_t before = __popc(peers & lt);
             const int top = 31 - __clz(peers);  // highest peer lane leads; its `before` + 1 is the group size
@@ -401,29 +438,93 @@ __global__ void __launch_bounds__(THREADS, MINB)
                 }
                 st_relaxed(&desc[(size_t)cur * RADIX + tid], DESC_INCL | (excl + my_count));
             }
-            const uint32_t gbase = base[tid];
-            s.tile_offs[tid] = gbase + excl - my_start;
-            if (base_next && cur == ntiles - 1) base_next[tid] = gbase + excl + my_count;
+            if (PTR_OUT) {
+                const unsigned long long gptr = static_cast<const unsigned long long *>(base_v)[tid];
+                s.tile_ptr[tid] = gptr + 4ull * (unsigned long long)excl - 4ull * (unsigned long long)my_start;
+            } else {
+                const uint32_t gbase = static_cast<const uint32_t *>(base_v)[tid];
+                s.tile_offs[tid] = gbase + excl - my_start;
+                if (base_next && cur == ntiles - 1) base_next[tid] = gbase + excl + my_count;
+            }
         }
         __syncthreads();
 
         // (7) coalesced write-out: consecutive threads, consecutive sorted keys
+        auto put = [&](uint32_t p) {
+            const uint32_t k = s.keys[buf][p];
+            const uint32_t d = binner.bin(k);
+            if (PTR_OUT) *reinterpret_cast<uint32_t *>(s.tile_ptr[d] + 4ull * p) = k;
+            else out[s.tile_offs[d] + p] = k;
+        };
         if (valid == TILE) {
 #pragma unroll
-            for (int i = 0; i < KPT; i++) {
-                const uint32_t p = tid + i * THREADS;
-                const uint32_t k = s.keys[buf][p];
-                out[s.tile_offs[digit_of(k, shift, mask)] + p] = k;
-            }
+            for (int i = 0; i < KPT; i++) put(tid + i * THREADS);
         } else {
-            for (uint32_t p = tid; p < valid; p += THREADS) {
-                const uint32_t k = s.keys[buf][p];
-                out[s.tile_offs[digit_of(k, shift, mask)] + p] = k;
-            }
+            for (uint32_t p = tid; p < valid; p += THREADS) put(p);
         }
         __syncthreads();
         cur = s.next_tile[buf ^ 1];
     }
+}
+
+// ------------------------------------------------------- distributed sort --
+// Pseudo-random sample of the local shard (splitter selection).
+__global__ void k_sample(const uint32_t *__restrict__ in, uint32_t n, uint32_t *__restrict__ out, uint32_t nsamples,
+                         uint32_t seed)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nsamples) return;
+    // stratified: one draw from each of nsamples equal strata (a multiply-xorshift hash picks the slot)
+    uint32_t h = (i + seed) * 0x9E3779B1u;
+    h ^= h >> 15; h *= 0x85EBCA77u; h ^= h >> 13;
+    const unsigned long long lo = (unsigned long long)i * n / nsamples, hi = (unsigned long long)(i + 1) * n / nsamples;
+    const unsigned long long span = hi > lo ? hi - lo : 1;
+    out[i] = in[lo + h % span];
+}
+
+// Keys per destination rank (bank-private counters: lane l owns column l).
+struct PtrTable { unsigned long long p[MAX_SPLITTERS + 1]; };
+__global__ void __launch_bounds__(1024, 1) k_dest_hist(const uint32_t *__restrict__ in, size_t n, const SplitBinner::Arg arg,
+                                                      uint32_t *__restrict__ counts)
+{
+    const SplitBinner binner(arg);
+    __shared__ uint32_t cnt[MAX_SPLITTERS + 1][32];
+    for (int i = threadIdx.x; i < (MAX_SPLITTERS + 1) * 32; i += blockDim.x) (&cnt[0][0])[i] = 0;
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31;
+    size_t head = ((16u - (reinterpret_cast<uintptr_t>(in) & 15u)) & 15u) >> 2;
+    if (head > n) head = n;
+    const size_t nvec = (n - head) >> 2, tail0 = head + (nvec << 2);
+    const size_t gtid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, gstride = (size_t)gridDim.x * blockDim.x;
+    if (gtid < head) atomicAdd(&cnt[binner.bin(in[gtid])][lane], 1u);
+    if (gtid < n - tail0) atomicAdd(&cnt[binner.bin(in[tail0 + gtid])][lane], 1u);
+    const uint4 *vin = reinterpret_cast<const uint4 *>(in + head);
+    for (size_t i = gtid; i < nvec; i += gstride) {
+        const uint4 v = ld_stream_v4(vin + i);
+        atomicAdd(&cnt[binner.bin(v.x)][lane], 1u);
+        atomicAdd(&cnt[binner.bin(v.y)][lane], 1u);
+        atomicAdd(&cnt[binner.bin(v.z)][lane], 1u);
+        atomicAdd(&cnt[binner.bin(v.w)][lane], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x <= (unsigned)binner.nsplit) {
+        uint32_t c = 0;
+        for (int l = 0; l < 32; l++) c += cnt[threadIdx.x][(l + lane) & 31];
+        if (c) atomicAdd(&counts[threadIdx.x], c);
+    }
+}
+
+// splitters[g] = the g/P quantile of the sorted all-rank sample.
+__global__ void k_pick_splitters(const uint32_t *__restrict__ sorted, uint32_t nsorted, int nranks,
+                                 uint32_t *__restrict__ splitters)
+{
+    const int g = threadIdx.x + 1;
+    if (g < nranks) splitters[g - 1] = sorted[(unsigned long long)g * nsorted / nranks];
+}
+
+__global__ void k_store_ptrs(const PtrTable t, unsigned long long *__restrict__ dst)
+{
+    if (threadIdx.x <= MAX_SPLITTERS) dst[threadIdx.x] = t.p[threadIdx.x];
 }
 
 // ------------------------------------------------------------ boundaries --

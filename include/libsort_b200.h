@@ -51,6 +51,45 @@ LIBSORT_API int libsortDeviceSort(const uint32_t *d_in, uint32_t *d_out, uint32_
                                   uint32_t width, uint32_t *d_boundaries, int boundary_mode, void *d_workspace,
                                   size_t workspace_bytes, void *stream, LibsortKernelTimes *times);
 
+/*
+ * Building blocks of the one-rank-per-GPU distributed sort that replaces the
+ * reference's host-mediated LSD shuffle (localTest/benchmarks.cpp:70-160,
+ * benchmark/pkg/sort/distrib.go:90-179).  The collectives themselves (count
+ * all-gather, optional NCCL all-to-all) are issued by the host side over
+ * torch.distributed; see gpu-radix-sort_b200/distrib.py.
+ *
+ * libsortDeviceSample:        nsamples stratified pseudo-random keys of the shard.
+ * libsortDevicePickSplitters: d_splitters[g-1] = g/nranks quantile of a sorted sample.
+ * libsortDeviceSplitCounts:   d_counts[0..nsplit] (16 words) = keys per
+ *     destination; destination of a key = number of splitters <= key
+ *     (splitters: DEVICE array, ascending, nsplit <= 15).
+ * libsortDeviceScatterToPeers: stable partition by destination written straight
+ *     to dest_ptrs[0..nsplit] (splitters: DEVICE array; dest_ptrs: HOST array of device addresses, local or
+ *     cudaIpc/NVLink-mapped peer memory): partition + key exchange in one
+ *     kernel.  n < 2^30; workspace as for libsortDeviceSort.
+ * libsortIpc*: peer-mappable allocations and cudaIpc handle plumbing (64-byte
+ *     handles) so ranks in different processes can map each other's receive
+ *     buffers.
+ */
+LIBSORT_API int libsortDeviceSample(const uint32_t *d_in, size_t n, uint32_t *d_out, uint32_t nsamples, uint32_t seed,
+                                    void *stream);
+LIBSORT_API int libsortDevicePickSplitters(const uint32_t *d_sorted, size_t nsorted, int nranks, uint32_t *d_splitters,
+                                           void *stream);
+LIBSORT_API int libsortDeviceSplitCounts(const uint32_t *d_in, size_t n, const uint32_t *splitters, int nsplit,
+                                         uint32_t *d_counts, void *stream);
+LIBSORT_API int libsortDeviceScatterToPeers(const uint32_t *d_in, size_t n, const uint32_t *splitters, int nsplit,
+                                            const unsigned long long *dest_ptrs, void *d_workspace,
+                                            size_t workspace_bytes, void *stream);
+LIBSORT_API int libsortIpcAlloc(size_t bytes, void **ptr);
+LIBSORT_API int libsortIpcFree(void *ptr);
+LIBSORT_API int libsortIpcExport(void *ptr, void *handle64);
+LIBSORT_API int libsortIpcOpen(const void *handle64, void **ptr);
+LIBSORT_API int libsortIpcClose(void *ptr);
+
+/* populateInput at an explicit stream position: arr[i] = element first+i of the
+ * fresh-process PCG sequence (reference libsort/utils.cu:63-79).  Thread safe. */
+LIBSORT_API void libsortPopulateInputAt(uint32_t *arr, size_t nelem, uint64_t first);
+
 /* Number of GPUs in the pool (0 before initLibSort). */
 LIBSORT_API int libsortDeviceCount(void);
 
