@@ -269,8 +269,7 @@ def run_multi(args, rank, world, local_rank):
     dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     n = args.keys
     # one continuous PCG stream; rank g owns elements [g*n, (g+1)*n)  
-    from oracle import oracle as o   # input generation only (jump-ahead of the stream); never timed
-    d_in = distrib.shard_of_pcg_stream(rank, n)
+    d_in = distrib.shard_of_pcg_stream(rank, n, args.dist)
     sorter = distrib.DistributedSorter(n, dist.group.WORLD, mode=args.exchange)
     for _ in range(max(args.warmup, 3)):
         sorter.sort(d_in)
@@ -301,7 +300,7 @@ def run_multi(args, rank, world, local_rank):
             "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u32", "data": "synthetic",
             "config": {"workload": "distributed uint32 sort, 2^28 keys per GPU (BASELINE configs[3] shape)",
-                       "keys_per_gpu": n, "keys_total": total, "exchange": args.exchange,
+                       "keys_per_gpu": n, "keys_total": total, "exchange": args.exchange, "distribution": args.dist,
                        "parallelism": "key-range sharding, 1 rank/GPU, MSD bucketing + exchange + local LSD",
                        "l2": "1 GiB shard per step per GPU, larger than L2"},
             "clocks": clk, "verify": stats, "phases_ms": phases,
@@ -328,6 +327,8 @@ def main():
     ap.add_argument("--keys", type=int, default=N_PER_GPU, help="keys per GPU")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
                     help="multi-GPU key exchange: fused scatter into peer memory, or NCCL all-to-all")
+    ap.add_argument("--dist", default="uniform", choices=["uniform", "zipf", "consthigh", "consthigh16"],
+                    help="multi-GPU input distribution (BASELINE configs[4] skew cases)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -1,0 +1,300 @@
+"""One-rank-per-GPU distributed uint32 sort over NVLink.
+
+Replaces the reference's host-mediated, 32/w-step LSD shuffle
+(localTest/benchmarks.cpp:70-160; benchmark/pkg/sort/distrib.go:90-179) with a
+single exchange:
+
+  1. sample the shard (k_sample), all-gather the samples (NCCL), sort them with
+     the device sort and take the g/P quantiles as splitters (on device)
+  2. count keys per destination (k_dest_hist), all-gather the P x P count
+     matrix (NCCL) -> receive layout
+  3. exchange, one of
+       p2p : ONE kernel partitions the shard and stores every key straight into
+             its destination GPU's receive buffer through cudaIpc/NVLink-mapped
+             pointers (k_onesweep<SplitBinner, PTR_OUT>) -- partition + all-to-all fused
+       nccl: partition locally with the same kernel, then NCCL all_to_all_single
+  4. local LSD sort of what arrived (libsortDeviceSort, 4 passes)
+
+Rank r ends up with the r-th value range, ascending.  torch.distributed is the
+plumbing (collectives, rendezvous); all key movement and sorting on the GPU is
+libsort.so.  Equal keys always go to the same rank (no tie splitting yet), so a
+single value with more than N/P copies unbalances the output -- reported by
+verify() as `imbalance`.
+"""
+import ctypes
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import binding, distrib_plan
+from .binding import KernelTimes
+
+SAMPLES_PER_RANK = 1 << 15
+
+
+def _u32_to_i32(v64):
+    return torch.where(v64 >= (1 << 31), v64 - (1 << 32), v64).to(torch.int32)
+
+
+def shard_of_pcg_stream(rank, n, transform=None):
+    """Rank's shard [rank*n, (rank+1)*n) of the one continuous PCG input stream, on the GPU."""
+    h = np.empty(n, dtype=np.uint32)
+    binding.lib().libsortPopulateInputAt(h.ctypes.data, n, rank * n)
+    t = torch.from_numpy(h.view(np.int32)).cuda()
+    x = t.to(torch.int64) & 0xFFFFFFFF
+    if transform == "zipf":        # log-uniform: k = floor(2^(32 x / 2^32)) - 1   (SURVEY.md 8(d) c5 i)
+        k = torch.floor(torch.exp2(32.0 * x.to(torch.float64) / 4294967296.0)) - 1
+        t = _u32_to_i32(k.clamp_(0, 4294967295).to(torch.int64))
+    elif transform == "consthigh":  # 0xAB000000 | (x & 0x00FFFFFF)                 (c5 ii)
+        t = _u32_to_i32((x & 0x00FFFFFF) | 0xAB000000)
+    elif transform == "consthigh16":
+        t = _u32_to_i32((x & 0xFFFF) | 0xABCD0000)
+    elif transform not in (None, "uniform"):
+        raise ValueError(transform)
+    return t.contiguous()
+
+
+class _RawCuda:
+    def __init__(self, ptr, n):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<i4", "data": (ptr, False), "version": 2}
+
+
+def _as_tensor(ptr, n, device):
+    return torch.as_tensor(_RawCuda(ptr, n), device=device)
+
+
+class DistributedSorter:
+    def __init__(self, n_local_max, group=None, mode="p2p", slack=1.25):
+        self.group = group if group is not None else dist.group.WORLD
+        self.rank, self.world = dist.get_rank(self.group), dist.get_world_size(self.group)
+        if self.world > distrib_plan.MAX_RANKS:
+            raise ValueError("at most %d ranks" % distrib_plan.MAX_RANKS)
+        if mode not in ("p2p", "nccl"):
+            raise ValueError(mode)
+        self.mode = mode
+        self.lib = binding.lib()
+        self.dev = torch.device("cuda", torch.cuda.current_device())
+        self.n_max = n_local_max
+        self.cap = int(n_local_max * slack) + (1 << 16)
+        L, dev, i32 = self.lib, self.dev, torch.int32
+        # receive buffer: own cudaMalloc so that its cudaIpc handle maps at offset 0
+        p = ctypes.c_void_p()
+        binding.check(L.libsortIpcAlloc(self.cap * 4, ctypes.byref(p)), "libsortIpcAlloc")
+        self.recv_ptr = p.value
+        self.recv = _as_tensor(self.recv_ptr, self.cap, dev)
+        self.peer_ptrs = [self.recv_ptr] * self.world
+        self._opened = []
+        if mode == "p2p" and self.world > 1:
+            handle = (ctypes.c_uint8 * 64)()
+            binding.check(L.libsortIpcExport(self.recv_ptr, handle), "libsortIpcExport")
+            mine = torch.tensor(list(handle), dtype=torch.uint8, device=dev)
+            allh = torch.empty(self.world * 64, dtype=torch.uint8, device=dev)
+            dist.all_gather_into_tensor(allh, mine, group=self.group)
+            allh = allh.cpu().numpy().reshape(self.world, 64)
+            for r in range(self.world):
+                if r == self.rank:
+                    continue
+                q = ctypes.c_void_p()
+                buf = (ctypes.c_uint8 * 64)(*allh[r].tolist())
+                binding.check(L.libsortIpcOpen(buf, ctypes.byref(q)), "libsortIpcOpen(rank %d)" % r)
+                self.peer_ptrs[r] = q.value
+                self._opened.append(q.value)
+        self.part = torch.empty(self.n_max, dtype=i32, device=dev) if mode == "nccl" else None
+        self.out = torch.empty(self.cap, dtype=i32, device=dev)
+        self.tmp = torch.empty(self.cap, dtype=i32, device=dev)
+        self.ws = torch.empty(L.libsortWorkspaceBytes(self.cap), dtype=torch.uint8, device=dev)
+        S = SAMPLES_PER_RANK
+        self.samples = torch.empty(S, dtype=i32, device=dev)
+        self.all_samples = torch.empty(S * self.world, dtype=i32, device=dev)
+        self.samples_sorted = torch.empty_like(self.all_samples)
+        self.samples_tmp = torch.empty_like(self.all_samples)
+        self.ws_small = torch.empty(L.libsortWorkspaceBytes(S * self.world), dtype=torch.uint8, device=dev)
+        self.splitters = torch.zeros(16, dtype=i32, device=dev)
+        self.counts = torch.zeros(16, dtype=i32, device=dev)
+        self.count_matrix = torch.zeros(16 * self.world, dtype=i32, device=dev)
+        self.token = torch.zeros(1, dtype=i32, device=dev)
+        self.h_counts = torch.empty(16 * self.world, dtype=i32).pin_memory()
+        self.seed = 1
+        # kernels per sort: sample, sample sort (hist, scan, 4 passes), pick, dest hist, store ptrs,
+        # scatter, local sort (hist, scan, 4 passes)
+        self.launches_per_sort = 1 + 6 + 1 + 1 + 1 + 1 + 6
+        self.last_totals = None
+
+    def close(self):
+        for p in self._opened:
+            self.lib.libsortIpcClose(p)
+        self._opened = []
+        if self.recv_ptr:
+            self.recv = None
+            self.lib.libsortIpcFree(self.recv_ptr)
+            self.recv_ptr = None
+
+    # ------------------------------------------------------------------ sort --
+    def _stream(self):
+        return torch.cuda.current_stream(self.dev).cuda_stream
+
+    def _plan(self, keys, ev=None):
+        """Steps 1-2: splitters on the device, count matrix on the host (the one host sync)."""
+        L, st, n, W = self.lib, self._stream(), keys.numel(), self.world
+        S = SAMPLES_PER_RANK
+        self.seed += 1
+        binding.check(L.libsortDeviceSample(keys.data_ptr(), n, self.samples.data_ptr(), S, self.seed, st), "sample")
+        if W > 1:
+            dist.all_gather_into_tensor(self.all_samples, self.samples, group=self.group)
+        else:
+            self.all_samples.copy_(self.samples)
+        binding.check(L.libsortDeviceSort(self.all_samples.data_ptr(), self.samples_sorted.data_ptr(),
+                                          self.samples_tmp.data_ptr(), S * W, 0, 32, None, 0, self.ws_small.data_ptr(),
+                                          self.ws_small.numel(), st, None), "sample sort")
+        binding.check(L.libsortDevicePickSplitters(self.samples_sorted.data_ptr(), S * W, W, self.splitters.data_ptr(), st),
+                      "pick splitters")
+        if ev:
+            ev("splitters")
+        binding.check(L.libsortDeviceSplitCounts(keys.data_ptr(), n, self.splitters.data_ptr(), W - 1,
+                                                 self.counts.data_ptr(), st), "split counts")
+        if W > 1:
+            dist.all_gather_into_tensor(self.count_matrix, self.counts, group=self.group)
+        else:
+            self.count_matrix.copy_(self.counts)
+        self.h_counts.copy_(self.count_matrix, non_blocking=True)
+        torch.cuda.current_stream(self.dev).synchronize()
+        cm = self.h_counts.numpy().reshape(W, 16)[:, :W].astype(np.int64)
+        if ev:
+            ev("counts")
+        return cm
+
+    def sort(self, keys, ev=None, times=None):
+        """Sort the union of all ranks' `keys`; returns (tensor view of this rank's range, its length)."""
+        if keys.dtype not in (torch.int32, torch.uint32) or not keys.is_cuda or not keys.is_contiguous():
+            raise ValueError("keys must be a contiguous CUDA int32/uint32 tensor")
+        L, st, n, W, me = self.lib, self._stream(), keys.numel(), self.world, self.rank
+        if n > self.n_max:
+            raise ValueError("shard larger than the sorter was built for")
+        cm = self._plan(keys, ev)
+        offsets, totals = distrib_plan.recv_layout(cm)
+        self.last_totals = totals
+        if int(totals.max()) > self.cap:
+            raise RuntimeError("receive buffer too small: %d keys arrive, capacity %d (raise slack)" % (int(totals.max()), self.cap))
+        nrecv = int(totals[me])
+        ptrs = (ctypes.c_uint64 * W)()
+        if self.mode == "p2p":
+            for r in range(W):
+                ptrs[r] = self.peer_ptrs[r] + 4 * int(offsets[me][r])
+        else:
+            send_off = np.cumsum(cm[me]) - cm[me]
+            for r in range(W):
+                ptrs[r] = self.part.data_ptr() + 4 * int(send_off[r])
+        binding.check(L.libsortDeviceScatterToPeers(keys.data_ptr(), n, self.splitters.data_ptr(), W - 1, ptrs,
+                                                    self.ws.data_ptr(), self.ws.numel(), st), "scatter")
+        if W > 1:
+            if self.mode == "p2p":
+                # stream-ordered barrier: nobody starts sorting before every rank's stores have landed
+                dist.all_reduce(self.token, group=self.group)
+            else:
+                dist.all_to_all_single(self.recv[:nrecv], self.part[:n], output_split_sizes=cm[:, me].tolist(),
+                                       input_split_sizes=cm[me].tolist(), group=self.group)
+        if ev:
+            ev("exchange")
+        binding.check(L.libsortDeviceSort(self.recv_ptr, self.out.data_ptr(), self.tmp.data_ptr(), nrecv, 0, 32, None, 0,
+                                          self.ws.data_ptr(), self.ws.numel(), st,
+                                          ctypes.byref(times) if times is not None else None), "local sort")
+        if W > 1 and self.mode == "p2p":
+            # the receive buffer is overwritten by the next sort's remote stores: fence it
+            dist.all_reduce(self.token, group=self.group)
+        if ev:
+            ev("local_sort")
+        return self.out[:nrecv], nrecv
+
+    # ---------------------------------------------------------- verification --
+    def verify(self, keys, out, nrecv):
+        """Size-independent properties of a distributed sort: every rank's range is
+        ascending, ranges are ordered across ranks, and the multiset is preserved
+        (sum / sum of squares mod p / count, all-reduced)."""
+        W = self.world
+        o64 = out.to(torch.int64) & 0xFFFFFFFF
+        i64 = keys.to(torch.int64) & 0xFFFFFFFF
+        asc = bool((o64[1:] >= o64[:-1]).all()) if nrecv > 1 else True
+        lo = int(o64[0]) if nrecv else (1 << 32)
+        hi = int(o64[-1]) if nrecv else -1
+        edge = torch.tensor([lo, hi, nrecv, int(asc)], dtype=torch.int64, device=self.dev)
+        edges = torch.empty(4 * W, dtype=torch.int64, device=self.dev)
+        fp = torch.stack([i64.sum(), (i64 * i64 % 1000003).sum(), torch.tensor(keys.numel(), device=self.dev),
+                          o64.sum(), (o64 * o64 % 1000003).sum(), torch.tensor(nrecv, device=self.dev)]).to(torch.int64)
+        if W > 1:
+            dist.all_gather_into_tensor(edges, edge, group=self.group)
+            dist.all_reduce(fp, group=self.group)
+        else:
+            edges.copy_(edge)
+        e = edges.cpu().numpy().reshape(W, 4)
+        fp = fp.cpu().numpy()
+        ordered, prev_hi = True, -1
+        for r in range(W):
+            if e[r][2] == 0:
+                continue
+            ordered &= bool(e[r][0] >= prev_hi)
+            prev_hi = int(e[r][1])
+        ok = bool(e[:, 3].all()) and ordered and bool((fp[:3] == fp[3:]).all())
+        if not ok:
+            raise AssertionError("distributed sort verification failed: edges=%s fp=%s" % (e.tolist(), fp.tolist()))
+        counts = e[:, 2].tolist()
+        return {"ok": True, "keys_per_rank": counts, "imbalance": distrib_plan.imbalance(counts)}
+
+    def phase_times(self, keys):
+        """CUDA-event time of each phase of one sort (ms, max over ranks)."""
+        marks = []
+
+        def ev(name):
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            marks.append((name, e))
+        if self.world > 1:
+            dist.barrier(group=self.group)
+        torch.cuda.synchronize()
+        ev("start")
+        kt = KernelTimes()
+        self.sort(keys, ev=ev, times=kt)
+        torch.cuda.synchronize()
+        names = [m[0] for m in marks[1:]]
+        vals = torch.tensor([marks[i][1].elapsed_time(marks[i + 1][1]) for i in range(len(marks) - 1)],
+                            dtype=torch.float64, device=self.dev)
+        passes = [kt.pass_ms[i] for i in range(kt.npass)]
+        nrecv = int(self.last_totals[self.rank])
+        extra = torch.tensor([sum(passes) / max(len(passes), 1), kt.histogram_ms], dtype=torch.float64, device=self.dev)
+        if self.world > 1:
+            dist.all_reduce(vals, op=dist.ReduceOp.MAX, group=self.group)
+            dist.all_reduce(extra, op=dist.ReduceOp.MAX, group=self.group)
+        res = {k + "_ms": float(v) for k, v in zip(names, vals.tolist())}
+        pass_ms = float(extra[0])
+        res["local_pass_ms"] = pass_ms
+        res["pass_gbs"] = 8.0 * nrecv / (pass_ms * 1e-3) / 1e9 if pass_ms > 0 else None
+        return res
+
+    def e2e(self, args, keys):
+        """Same sort with HOST shards: pinned H2D of the shard and D2H of the sorted range
+        inside the timed region (wall clock, max over ranks)."""
+        import time
+        n = keys.numel()
+        h_in = keys.cpu().pin_memory()
+        h_out = torch.empty(self.cap, dtype=torch.int32).pin_memory()
+        d_in = torch.empty_like(keys)
+        steps = max(1, min(args.steps, 5))
+        tot = 0.0
+        for it in range(steps + 1):
+            if self.world > 1:
+                dist.barrier(group=self.group)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            d_in.copy_(h_in, non_blocking=True)
+            out, nrecv = self.sort(d_in)
+            h_out[:nrecv].copy_(out, non_blocking=True)
+            torch.cuda.synchronize()
+            dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=self.dev)
+            if self.world > 1:
+                dist.all_reduce(dt, op=dist.ReduceOp.MAX, group=self.group)
+            if it > 0:
+                tot += float(dt)
+        total_keys = n * self.world
+        return {"value": total_keys * steps / tot / 1e9, "unit": "Gkeys/s", "h2d_bytes_per_step": 4 * total_keys,
+                "d2h_bytes_per_step": 4 * total_keys, "ms_per_step": tot / steps * 1e3, "steps": steps,
+                "api": "DistributedSorter.sort with pinned host shards"}

@@ -1,0 +1,87 @@
+"""Worker for the multi-process tests: run under torchrun.
+   gloo mode (CPU): exercises the host-side plan (splitters, count matrix, receive layout)
+                    with numpy standing in for the device kernels.
+   nccl mode (GPU): runs DistributedSorter end to end and checks it against the oracle."""
+import importlib
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oracle import oracle as o  # noqa: E402
+
+
+def shard(rank, n, kind):
+    x = o.pcg_stream((rank + 1) * n)[rank * n:]
+    if kind == "consthigh":
+        x = (np.uint32(0xAB000000) | (x & np.uint32(0x00FFFFFF))).astype(np.uint32)
+    elif kind == "zipf":
+        x = (np.floor(2.0 ** (32.0 * x.astype(np.float64) / 2.0 ** 32)) - 1).astype(np.uint32)
+    elif kind == "fewvalues":
+        x = (x % np.uint32(5)).astype(np.uint32) * np.uint32(1000)
+    return x
+
+
+def main():
+    mode, n = sys.argv[1], int(sys.argv[2])
+    plan = importlib.import_module("gpu-radix-sort_b200.distrib_plan")
+    if mode == "gloo":
+        dist.init_process_group("gloo")
+        rank, world = dist.get_rank(), dist.get_world_size()
+        for kind in ("uniform", "consthigh", "zipf", "fewvalues"):
+            keys = shard(rank, n, kind)
+            sample = torch.from_numpy(keys[:: max(1, n // 256)][:256].astype(np.int64))
+            gathered = [torch.empty_like(sample) for _ in range(world)]
+            dist.all_gather(gathered, sample)
+            spl = plan.choose_splitters(np.sort(torch.cat(gathered).numpy().astype(np.uint32)), world)
+            dest = plan.destination(keys, spl)
+            cnt = torch.from_numpy(np.bincount(dest, minlength=world).astype(np.int64))
+            rows = [torch.empty_like(cnt) for _ in range(world)]
+            dist.all_gather(rows, cnt)
+            cm = torch.stack(rows).numpy()
+            offsets, totals = plan.recv_layout(cm)
+            assert totals.sum() == n * world and (offsets[0] == 0).all()
+            assert (offsets[-1] + cm[-1] == totals).all()
+            # exchange with all_to_all, then local sort: rank r must hold the r-th value range
+            order = np.argsort(dest, kind="stable")
+            send = [keys[order][dest[order] == r] for r in range(world)]
+            everyone = [None] * world                      # gloo has no all-to-all: gather and pick our column
+            dist.all_gather_object(everyone, send)
+            recv = [everyone[s][rank] for s in range(world)]
+            assert [len(x) for x in recv] == cm[:, rank].tolist()
+            mine = np.sort(np.concatenate(recv).astype(np.uint32))
+            allkeys = np.sort(np.concatenate([shard(r, n, kind) for r in range(world)]))
+            start = int(totals[:rank].sum())
+            assert np.array_equal(mine, allkeys[start:start + mine.size]), kind
+        print("rank %d gloo plan ok" % rank)
+    else:
+        local = int(os.environ.get("LOCAL_RANK", "0"))
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        rank, world = dist.get_rank(), dist.get_world_size()
+        distrib = importlib.import_module("gpu-radix-sort_b200.distrib")
+        for exch in ("p2p", "nccl"):
+            sorter = distrib.DistributedSorter(n, mode=exch, slack=2.5)
+            for kind in ("uniform", "consthigh", "zipf"):
+                keys = shard(rank, n, kind)
+                d = torch.from_numpy(keys.view(np.int32)).cuda()
+                for rep in range(2):
+                    out, cnt = sorter.sort(d)
+                stats = sorter.verify(d, out, cnt)
+                allkeys = np.sort(np.concatenate([shard(r, n, kind) for r in range(world)]))
+                start = int(sum(stats["keys_per_rank"][:rank]))
+                got = out.cpu().numpy().view(np.uint32)
+                assert np.array_equal(got, allkeys[start:start + cnt]), (exch, kind)
+                if rank == 0:
+                    print(exch, kind, "ok; keys/rank", stats["keys_per_rank"], "imbalance %.3f" % stats["imbalance"])
+            sorter.close()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,51 @@
+"""Distributed sort: host-side plan on CPU (gloo, world size 2 and 3) and the
+full NCCL/NVLink path on GPUs (needs >= 2 devices)."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+WORKER = os.path.join(ROOT, "tests", "dist_worker.py")
+
+
+def torchrun(nproc, port, *args, timeout=300):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nproc),
+           "--master-addr", "127.0.0.1", "--master-port", str(port), WORKER] + [str(a) for a in args]
+    return subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, cwd=ROOT)
+
+
+def test_plan_functions(pkg):
+    import importlib
+    plan = importlib.import_module(pkg.__name__ + ".distrib_plan")
+    s = np.arange(0, 1000, dtype=np.uint32)
+    spl = plan.choose_splitters(s, 4)
+    assert spl.tolist() == [250, 500, 750]
+    d = plan.destination(np.array([0, 249, 250, 999, 500], np.uint32), spl)
+    assert d.tolist() == [0, 0, 1, 3, 2]          # a key equal to a splitter goes right (SplitBinner::bin)
+    off, tot = plan.recv_layout([[1, 2], [3, 4]])
+    assert off.tolist() == [[0, 0], [1, 2]] and tot.tolist() == [4, 6]
+    assert plan.imbalance([4, 6]) == pytest.approx(1.2)
+    with pytest.raises(ValueError):
+        plan.choose_splitters(s, 17)
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_plan_over_gloo(world):
+    r = torchrun(world, 29731 + world, "gloo", 20000)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    assert r.stdout.count("gloo plan ok") == world
+
+
+@pytest.mark.gpu
+def test_distributed_sort_on_gpus():
+    import torch
+    ndev = torch.cuda.device_count()
+    if ndev < 2:
+        pytest.skip("needs >= 2 GPUs")
+    world = 2 if ndev < 4 else 4
+    r = torchrun(world, 29741, "nccl", 300000, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    assert r.stdout.count(" ok; keys/rank") == 6
