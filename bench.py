@@ -266,7 +266,8 @@ def run_multi(args, rank, world, local_rank):
     pkg = importlib.import_module("gpu-radix-sort_b200")
     distrib = importlib.import_module("gpu-radix-sort_b200.distrib")
     torch.cuda.set_device(local_rank)
-    dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    import datetime
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank), timeout=datetime.timedelta(seconds=180))
     n = args.keys
     # one continuous PCG stream; rank g owns elements [g*n, (g+1)*n)  
     d_in = distrib.shard_of_pcg_stream(rank, n, args.dist)
@@ -291,6 +292,7 @@ def run_multi(args, rank, world, local_rank):
     clk = clocks.stop()
     stats = sorter.verify(d_in, out, cnt)           # sortedness, rank ordering, multiset fingerprint
     phases = sorter.phase_times(d_in)               # per-phase CUDA-event times, max over ranks
+    e2e = sorter.e2e(args, d_in)                    # collective: every rank takes part
     if rank == 0:
         peak, peak_src = measured_peak()
         total = n * world
@@ -311,7 +313,7 @@ def run_multi(args, rank, world, local_rank):
             "nvlink": {"bytes_out_per_gpu": exch_bytes, "exchange_ms": phases.get("exchange_ms"),
                        "gbs_per_direction": exch_bytes / (phases["exchange_ms"] * 1e-3) / 1e9 if phases.get("exchange_ms") else None,
                        "peak_gbs": 770.0, "peak_source": "measured peer copy per direction (B200_PROFILING.md)"},
-            "e2e": sorter.e2e(args, d_in),
+            "e2e": e2e,
         }
         print(json.dumps(line), flush=True)
     dist.barrier()

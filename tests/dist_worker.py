@@ -61,7 +61,8 @@ def main():
     else:
         local = int(os.environ.get("LOCAL_RANK", "0"))
         torch.cuda.set_device(local)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        import datetime
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=datetime.timedelta(seconds=120))
         rank, world = dist.get_rank(), dist.get_world_size()
         distrib = importlib.import_module("gpu-radix-sort_b200.distrib")
         for exch in ("p2p", "nccl"):
