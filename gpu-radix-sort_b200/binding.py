@@ -33,8 +33,11 @@ def build(verbose=False):
     res = subprocess.run(["make", "-C", _CSRC, "all", "tools"], capture_output=True, text=True)
     if res.returncode != 0:
         raise RuntimeError("libsort build failed:\n" + res.stdout[-4000:] + res.stderr[-4000:])
+    res2 = subprocess.run(["make", "-C", os.path.join(_HERE, "localTest")], capture_output=True, text=True)
+    if res2.returncode != 0:
+        raise RuntimeError("localTest build failed:\n" + res2.stdout[-2000:] + res2.stderr[-2000:])
     if verbose:
-        print(res.stdout)
+        print(res.stdout, res2.stdout)
     return lib_path()
 
 

@@ -213,3 +213,17 @@ def test_pylibsort_wrapper(gpu_lib, oracle, pkg):
     caps = np.diff(np.array(bounds, dtype=np.int64) * 4, append=len(buf))    # data.py:301-304
     pls.checkPartial(k.tobytes(), buf, caps, 4, 8)
     assert len(pls.generateInputs(10)) == 40
+
+
+def test_cxx_consumers(gpu_lib, pkg):
+    """BASELINE configs[0]: localTest ./radix_sort, 1M keys, GPU sort vs the CPU local sort;
+    and the reference's own unmodified harness linked against our libsort.so."""
+    import subprocess
+    exe = os.path.join(os.path.dirname(pkg.__file__), "localTest", "radix_sort")
+    for n in ("1048576", "1111"):
+        r = subprocess.run([exe, n], capture_output=True, text=True, timeout=120)
+        assert r.returncode == 0 and "Success!" in r.stdout, r.stdout + r.stderr
+    ref_exe = os.path.join(os.path.dirname(os.path.dirname(__file__)), "oracle", "_ref", "radix_sort_reference_harness")
+    if os.path.exists(ref_exe):
+        r = subprocess.run([ref_exe], capture_output=True, text=True, timeout=300)   # runBenches(): 16-bit partial, 2^28 keys
+        assert r.returncode == 0 and "Partial sort (16b)" in r.stdout, r.stdout + r.stderr
