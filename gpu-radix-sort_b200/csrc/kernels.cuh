@@ -410,6 +410,16 @@ __global__ void __launch_bounds__(THREADS, MINB)
         // (5) rank: position of every key in the digit-sorted tile
         uint32_t pos[KPT];
         const uint32_t my_hist = smem_u32(&s.warp_hist[warp][0]);
+#if defined(SORT_EXPERIMENT_RANK_ATOMS)
+        // EXPERIMENT ONLY (never the shipped default): rank straight from the returning
+        // shared atomic, relying on the hardware serving colliding lanes in lane order.
+#pragma unroll
+        for (int i = 0; i < KPT; i++) {
+            pos[i] = atomicAdd(&s.warp_hist[warp][binner.bin(key[i])], 1u);
+            __syncwarp();
+        }
+        (void)lt; (void)my_hist; (void)nbits;
+#else
 #pragma unroll
         for (int i = 0; i < KPT; i++) {
             const uint32_t d = binner.bin(key[i]);
@@ -420,6 +430,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
             off = __shfl_sync(0xffffffffu, off, top);
             pos[i] = off + before;
         }
+#endif
         // every warp has its keys in registers since (3); the staging buffer can be overwritten
 #pragma unroll
         for (int i = 0; i < KPT; i++) s.keys[buf][pos[i]] = key[i];

@@ -69,6 +69,44 @@ __global__ void k_read(const uint4 *in, uint32_t *out, size_t n)
     if (acc == 0x12345) out[0] = acc;
 }
 
+
+// Same-address shared-memory atomics inside ONE warp instruction: in which
+// order does the hardware serve the colliding lanes?  Every lane adds 1 to the
+// counter of a random digit and gets the old value back; among the lanes that
+// named the same counter the returned values are consecutive, and this kernel
+// counts how often they are NOT in ascending lane order.  SHARED = 1: all
+// warps of the CTA use one counter array (cross-warp contention in flight).
+template <int SHARED>
+__global__ void k_atoms_order(unsigned long long *out, int bits, int iters)
+{
+    __shared__ uint32_t h[32][256];
+    for (int i = threadIdx.x; i < 32 * 256; i += blockDim.x) (&h[0][0])[i] = 0;
+    __syncthreads();
+    uint32_t *my = SHARED ? h[0] : h[threadIdx.x >> 5];
+    const uint32_t lane = threadIdx.x & 31, lt = (1u << lane) - 1, m = (1u << bits) - 1;
+    uint32_t s = (threadIdx.x + 1) * 2654435761u + blockIdx.x * 97u;
+    unsigned long long bad = 0, pairs = 0;
+    for (int i = 0; i < iters; i++) {
+        uint32_t d = rng(s) & m;
+        if ((i & 7) == 7) d = (lane * 5 + i) & 1;          // heavy collisions now and then
+        const uint32_t r = atomicAdd(&my[d], 1u);
+        const uint32_t peers = __match_any_sync(0xffffffffu, d);
+        // the lowest peer lane must hold the smallest value and my value must be its value + my rank
+        const int first = __ffs(peers) - 1;
+        const uint32_t r0 = __shfl_sync(0xffffffffu, r, first);
+        const uint32_t want = r0 + __popc(peers & lt);
+        if (SHARED) {
+            // other warps interleave: only the relative order inside the warp is checked
+            const uint32_t prev_lane = 31 - __clz(peers & lt | 0u);
+            const uint32_t rp = __shfl_sync(0xffffffffu, r, (peers & lt) ? prev_lane : lane);
+            if ((peers & lt) && !(rp < r)) bad++;
+        } else if (r != want) bad++;
+        pairs += (peers & lt) ? 1 : 0;
+    }
+    atomicAdd(&out[0], bad);
+    atomicAdd(&out[1], pairs);
+}
+
 template <typename F> static void rate(const char *name, F launch, int threads, uint32_t *d_out, int blocks)
 {
     launch(); cudaDeviceSynchronize(); launch(); cudaDeviceSynchronize();
@@ -92,6 +130,19 @@ int main()
             rate("lds+sts rmw", [&] { k_smem<2><<<sms, threads>>>(d_out, bits); }, threads, d_out, 1);
             rate("sts random", [&] { k_smem<3><<<sms, threads>>>(d_out, bits); }, threads, d_out, 1);
         }
+    }
+    {
+        unsigned long long *d_cnt; cudaMalloc(&d_cnt, 16);
+        for (int shared = 0; shared < 2; shared++)
+            for (int bits : {8, 4, 1}) {
+                cudaMemset(d_cnt, 0, 16);
+                if (shared) k_atoms_order<1><<<sms * 2, 1024>>>(d_cnt, bits, 20000);
+                else k_atoms_order<0><<<sms * 2, 1024>>>(d_cnt, bits, 20000);
+                cudaError_t e = cudaDeviceSynchronize();
+                unsigned long long h[2]; cudaMemcpy(h, d_cnt, 16, cudaMemcpyDeviceToHost);
+                printf("atoms lane order  %s counters, %d-bit digits: %llu colliding lanes checked, %llu out of ascending lane order (%s)\n",
+                       shared ? "CTA-shared" : "warp-private", bits, h[1], h[0], cudaGetErrorString(e));
+            }
     }
     size_t n = (size_t)1 << 30;  // bytes
     uint4 *a, *b; cudaMalloc(&a, n); cudaMalloc(&b, n); cudaMemset(a, 1, n); cudaMemset(b, 2, n);
