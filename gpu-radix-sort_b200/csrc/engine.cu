@@ -6,19 +6,23 @@
 #include <atomic>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <mutex>
 
 namespace b200sort {
 
 // ---- compiled-in kernel variant -------------------------------------------
 #ifndef SORT_THREADS
-#define SORT_THREADS 512
+#define SORT_THREADS 256
 #endif
 #ifndef SORT_KPT
-#define SORT_KPT 16
+#define SORT_KPT 32
 #endif
 #ifndef SORT_MINB
-#define SORT_MINB 2
+#define SORT_MINB 4
+#endif
+#ifndef SORT_LB
+#define SORT_LB 2   // look-back descriptors fetched ahead of the ranking phase
 #endif
 #ifndef HIST_THREADS
 #define HIST_THREADS 512
@@ -28,7 +32,12 @@ namespace b200sort {
 #endif
 
 constexpr int kTile = SORT_THREADS * SORT_KPT;
-using SortSmem = OnesweepSmem<SORT_THREADS, SORT_KPT>;
+using SortSmem = OnesweepSmem<SORT_THREADS, SORT_KPT, false>;
+using SortSmemPtr = OnesweepSmem<SORT_THREADS, SORT_KPT, true>;
+
+template <int RANK, int NBITS, class Binner, bool PTR_OUT>
+using SortKernel = decltype(&k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, RANK, NBITS, SORT_LB, Binner, PTR_OUT>);
+#define SORT_KERNEL(RANK, NBITS, BINNER, PTR) k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, RANK, NBITS, SORT_LB, BINNER, PTR>
 
 int tile_keys() { return kTile; }
 
@@ -61,6 +70,7 @@ struct DevInfo {
     int sms = 0;
     int sort_occ = 0;
     int hist_occ = 0;
+    bool rank_atoms = false;  // rank keys with returning shared atomics (self-tested) instead of ballots
 };
 static DevInfo g_dev[64];
 static std::mutex g_dev_mu;
@@ -105,6 +115,37 @@ static cudaError_t launch_hist(const uint32_t *in, size_t n, const PassPlan &pla
     return cudaSuccess;
 }
 
+// LIBSORT_RANK = ballot | atoms | auto (default).  "atoms" ranks a key with the
+// value its warp's shared-memory atomicAdd returns, which is stable only if the
+// hardware serves the lanes of one instruction that hit the same address in
+// ascending lane order.  That is how sm_100 behaves (profiles/r01_atoms_lane_order.log:
+// 0 exceptions in 2x10^10 collisions) but it is not an architectural promise,
+// so `auto` first proves it on the device with k_selftest_atoms_order and
+// falls back to the ballot kernel (same results, more instructions) otherwise.
+static cudaError_t choose_rank_mode(int dev, bool *atoms)
+{
+    const char *e = getenv("LIBSORT_RANK");
+    if (e && !strcmp(e, "ballot")) { *atoms = false; return cudaSuccess; }
+    if (e && !strcmp(e, "atoms")) { *atoms = true; return cudaSuccess; }
+    unsigned long long *d_bad = nullptr, h_bad[2] = {0, 0};
+    cudaError_t err = cudaMalloc(&d_bad, sizeof(h_bad));
+    if (err != cudaSuccess) return err;
+    err = cudaMemset(d_bad, 0, sizeof(h_bad));
+    int sms = 1;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (err == cudaSuccess) {
+        k_selftest_atoms_order<<<sms, 1024>>>(d_bad, 256);
+        err = cudaMemcpy(h_bad, d_bad, sizeof(h_bad), cudaMemcpyDeviceToHost);
+    }
+    cudaFree(d_bad);
+    if (err != cudaSuccess) return err;
+    *atoms = (h_bad[0] == 0 && h_bad[1] > 0);
+    if (!*atoms)
+        fprintf(stderr, "libsort: device %d serves colliding shared atomics out of lane order (%llu of %llu); using ballot ranking\n",
+                dev, h_bad[0], h_bad[1]);
+    return cudaSuccess;
+}
+
 static cudaError_t dev_info(DevInfo **out)
 {
     int dev = 0;
@@ -116,14 +157,17 @@ static cudaError_t dev_info(DevInfo **out)
     if (!d.ready) {
         e = cudaDeviceGetAttribute(&d.sms, cudaDevAttrMultiProcessorCount, dev);
         if (e != cudaSuccess) return e;
-        auto kern = k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, 8, RadixBinner, false>;
-        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem));
+        auto kern = SORT_KERNEL(RANK_ATOMS, 0, RadixBinner, false);
+        const int sm = (int)sizeof(SortSmem), smp = (int)sizeof(SortSmemPtr);
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
         if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, 0, RadixBinner, false>,
-                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem));
+        e = cudaFuncSetAttribute(SORT_KERNEL(RANK_BALLOT, 8, RadixBinner, false), cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
         if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, 0, SplitBinner, true>,
-                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem));
+        e = cudaFuncSetAttribute(SORT_KERNEL(RANK_BALLOT, 0, RadixBinner, false), cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(SORT_KERNEL(RANK_ATOMS, 0, SplitBinner, true), cudaFuncAttributeMaxDynamicSharedMemorySize, smp);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(SORT_KERNEL(RANK_BALLOT, 0, SplitBinner, true), cudaFuncAttributeMaxDynamicSharedMemorySize, smp);
         if (e != cudaSuccess) return e;
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.sort_occ, kern, SORT_THREADS, sizeof(SortSmem));
         if (e != cudaSuccess) return e;
@@ -131,10 +175,12 @@ static cudaError_t dev_info(DevInfo **out)
                                                           HIST_THREADS, 0);
         if (e != cudaSuccess) return e;
         if (d.sort_occ < 1 || d.hist_occ < 1) return cudaErrorLaunchOutOfResources;
+        e = choose_rank_mode(dev, &d.rank_atoms);
+        if (e != cudaSuccess) return e;
         if (const char *dbg = getenv("LIBSORT_DEBUG"))
             if (dbg[0] == '1')
-                fprintf(stderr, "libsort: dev %d sms=%d tile=%d sort_occ=%d hist_occ=%d smem=%zu\n", dev, d.sms, kTile,
-                        d.sort_occ, d.hist_occ, sizeof(SortSmem));
+                fprintf(stderr, "libsort: dev %d sms=%d tile=%d sort_occ=%d hist_occ=%d smem=%zu rank=%s\n", dev, d.sms, kTile,
+                        d.sort_occ, d.hist_occ, sizeof(SortSmem), d.rank_atoms ? "atoms" : "ballot");
         d.ready = true;
     }
     *out = &d;
@@ -284,8 +330,9 @@ cudaError_t sort_bits(const uint32_t *in, uint32_t *a, uint32_t *b, uint32_t *wa
             const int grid = (int)std::min<size_t>(nt, (size_t)dev->sms * dev->sort_occ);
             uint32_t *bcur = base + ((q & 1) * MAX_PASSES + p) * RADIX;
             uint32_t *bnext = (q + 1 < nportions) ? base + (((q + 1) & 1) * MAX_PASSES + p) * RADIX : nullptr;
-            auto kern = plan.mask[p] == 0xffu ? k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, 8, RadixBinner, false>
-                                              : k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, 0, RadixBinner, false>;
+            auto kern = dev->rank_atoms          ? SORT_KERNEL(RANK_ATOMS, 0, RadixBinner, false)
+                        : plan.mask[p] == 0xffu ? SORT_KERNEL(RANK_BALLOT, 8, RadixBinner, false)
+                                                : SORT_KERNEL(RANK_BALLOT, 0, RadixBinner, false);
             kern<<<grid, SORT_THREADS, sizeof(SortSmem), st>>>(
                 src + k0, dst, (uint32_t)(k1 - k0), RadixBinner::Arg{plan.shift[p], plan.mask[p]}, bcur, bnext,
                 desc + ((size_t)p * ntiles + t0) * RADIX, tickets + p * MAX_PORTIONS + q, nt, use_tma);
@@ -374,9 +421,9 @@ cudaError_t scatter_by_splitters(const uint32_t *in, size_t n, const uint32_t *s
     k_store_ptrs<<<1, 32, 0, st>>>(t, d_ptrs);
     const int grid = (int)std::min<size_t>(ntiles, (size_t)dev->sms * dev->sort_occ);
     const int use_tma = (reinterpret_cast<uintptr_t>(in) & 15u) == 0;
-    k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, 0, SplitBinner, true><<<grid, SORT_THREADS, sizeof(SortSmem), st>>>(
-        in, nullptr, (uint32_t)n, SplitBinner::Arg{splitters, nsplit}, d_ptrs, nullptr, ws + WS_DESC, ws + WS_TICKET,
-        (uint32_t)ntiles, use_tma);
+    auto kern = dev->rank_atoms ? SORT_KERNEL(RANK_ATOMS, 0, SplitBinner, true) : SORT_KERNEL(RANK_BALLOT, 0, SplitBinner, true);
+    kern<<<grid, SORT_THREADS, sizeof(SortSmemPtr), st>>>(in, nullptr, (uint32_t)n, SplitBinner::Arg{splitters, nsplit}, d_ptrs,
+                                                          nullptr, ws + WS_DESC, ws + WS_TICKET, (uint32_t)ntiles, use_tma);
     return cudaGetLastError();
 }
 

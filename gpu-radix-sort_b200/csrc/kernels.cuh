@@ -18,6 +18,7 @@
 // gpu_glbl_shuffle (reference libsort/sort.cu:29-213, scan.cu) and k_bounds_*
 // replace gpu_groups + the host back-fill (sort.cu:14-27, 367-394).
 #pragma once
+#include <type_traits>
 #include "ptx.cuh"
 
 namespace b200sort {
@@ -243,6 +244,11 @@ struct RadixBinner {
     uint32_t shift, mask;
     __device__ __forceinline__ explicit RadixBinner(const Arg &a) : shift(a.shift), mask(a.mask) {}
     __device__ __forceinline__ uint32_t bin(uint32_t key) const { return (key >> shift) & mask; }
+    // 4 * bin(key) in two ALU ops: rotate the digit to bits [2, 10) and mask
+    __device__ __forceinline__ uint32_t bin4(uint32_t key) const
+    {
+        return __funnelshift_r(key, key, (shift + 30u) & 31u) & (mask << 2);
+    }
     __device__ __forceinline__ uint32_t pad_bin() const { return mask; }  // bin of the 0xffffffff padding keys
     __device__ __forceinline__ int nbits() const { return __popc(mask); }
 };
@@ -263,22 +269,27 @@ struct SplitBinner {
         for (int j = 0; j < MAX_SPLITTERS; j++) d += (j < nsplit && key >= v[j]) ? 1u : 0u;
         return d;
     }
+    __device__ __forceinline__ uint32_t bin4(uint32_t key) const { return bin(key) << 2; }
     __device__ __forceinline__ uint32_t pad_bin() const { return (uint32_t)nsplit; }
     __device__ __forceinline__ int nbits() const { return 32 - __clz(nsplit); }  // bins 0..nsplit
 };
 
-template <int THREADS, int KPT>
+template <int THREADS, int KPT, bool PTR_OUT>
 struct OnesweepSmem {
     static constexpr int TILE = THREADS * KPT;
     static constexpr int NWARPS = THREADS / 32;
-    alignas(128) uint32_t keys[2][TILE];       // TMA destinations, re-used for the sorted tile
-    uint32_t warp_hist[NWARPS][RADIX];         // per-warp digit counters -> running offsets
-    uint32_t tile_offs[RADIX];                 // global dst of bucket b minus its start in the tile
-    unsigned long long tile_ptr[RADIX];        // PTR_OUT: byte address of the same, possibly in peer memory
+    alignas(128) uint32_t keys[TILE];          // TMA landing buffer, then the digit-sorted tile
+    uint32_t warp_hist[NWARPS][RADIX];         // per-warp digit counters -> running BYTE offsets into keys[]
+    // global destination of bucket b minus its start in the tile: an index into `out`,
+    // or (PTR_OUT) a byte address, possibly in peer memory
+    typename std::conditional<PTR_OUT, unsigned long long, uint32_t>::type tile_dst[RADIX];
     uint32_t s_warp[8];
-    alignas(8) uint64_t mbar[2];
-    uint32_t next_tile[2];
+    alignas(8) uint64_t mbar;
+    uint32_t next_tile;
 };
+
+constexpr int RANK_BALLOT = 0;  // one vote.ballot per digit bit + a leader atomic: architecturally ordered
+constexpr int RANK_ATOMS = 1;   // rank = return value of the warp's shared atomic (see DESIGN.md "atomic ranking")
 
 // in/out: this portion's keys (n < 2^30 so that counts fit the 30-bit
 // descriptor value).  base: global bucket bases for this portion;
@@ -286,13 +297,18 @@ struct OnesweepSmem {
 // portion.  desc: ntiles x 256 zero-initialised descriptors; ticket: zeroed.
 // PTR_OUT: `base` holds one 64-bit destination pointer per bin (local or
 // NVLink-mapped peer memory) instead of an offset into `out`.
-template <int THREADS, int KPT, int MINB, int NBITS, class Binner, bool PTR_OUT>
+//
+// One tile per loop trip, one 1-D bulk TMA per tile.  The ticket for a tile is
+// taken only when the CTA is about to load it, so tiles publish their counts
+// in (nearly) ticket order and a look-back rarely meets an unpublished
+// predecessor; load latency is covered by the other CTAs resident on the SM.
+template <int THREADS, int KPT, int MINB, int RANK, int NBITS, int LB, class Binner, bool PTR_OUT>
 __global__ void __launch_bounds__(THREADS, MINB)
     k_onesweep(const uint32_t *__restrict__ in, uint32_t *__restrict__ out, uint32_t n, const typename Binner::Arg binner_arg,
                const void *__restrict__ base_v, uint32_t *__restrict__ base_next, uint32_t *__restrict__ desc,
                uint32_t *__restrict__ ticket, uint32_t ntiles, int use_tma)
 {
-    using Smem = OnesweepSmem<THREADS, KPT>;
+    using Smem = OnesweepSmem<THREADS, KPT, PTR_OUT>;
     constexpr int TILE = Smem::TILE;
     constexpr int NWARPS = Smem::NWARPS;
     static_assert(THREADS >= RADIX, "need one thread per bin");
@@ -300,67 +316,55 @@ __global__ void __launch_bounds__(THREADS, MINB)
     Smem &s = *reinterpret_cast<Smem *>(smem_raw);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t lt = lanemask_lt();
     const Binner binner(binner_arg);
-    const int nbits = binner.nbits();
     const uint32_t pad_bin = binner.pad_bin();
+    unsigned char *const my_hist = reinterpret_cast<unsigned char *>(s.warp_hist[warp]);
+    unsigned char *const tile_bytes = reinterpret_cast<unsigned char *>(s.keys);
 
-    auto issue_load = [&](uint32_t tile, int buf) {
+    auto issue_load = [&](uint32_t tile) {
         // elected thread: arm the barrier and start the bulk copy of the
         // 16 B-multiple part of the tile; a ragged tail (<= 3 keys, last tile
         // only) is read straight from global by its consumer.
         const uint32_t valid = min((uint32_t)TILE, n - tile * (uint32_t)TILE);
         const uint32_t bytes = (valid * 4u) & ~15u;
         if (bytes) {
-            mbar_arrive_expect_tx(&s.mbar[buf], bytes);
-            tma_load_1d(s.keys[buf], in + (size_t)tile * TILE, bytes, &s.mbar[buf]);
+            mbar_arrive_expect_tx(&s.mbar, bytes);
+            tma_load_1d(s.keys, in + (size_t)tile * TILE, bytes, &s.mbar);
         } else {
-            mbar_arrive_expect_tx(&s.mbar[buf], 0);
+            mbar_arrive_expect_tx(&s.mbar, 0);
         }
     };
 
     if (tid == 0) {
-        mbar_init(&s.mbar[0], 1);
-        mbar_init(&s.mbar[1], 1);
+        mbar_init(&s.mbar, 1);
         fence_mbar_init();
-        uint32_t t = atomicAdd(ticket, 1u);
-        s.next_tile[0] = t;
-        if (use_tma && t < ntiles) issue_load(t, 0);
+        const uint32_t t = atomicAdd(ticket, 1u);
+        s.next_tile = t;
+        if (use_tma && t < ntiles) issue_load(t);
     }
+#pragma unroll
+    for (int j = lane; j < RADIX; j += 32) s.warp_hist[warp][j] = 0;
     __syncthreads();
-    uint32_t cur = s.next_tile[0];
+    uint32_t cur = s.next_tile;
 
     for (uint32_t it = 0; cur < ntiles; ++it) {
-        const int buf = it & 1;
         const uint32_t tile_base = cur * (uint32_t)TILE;
         const uint32_t valid = min((uint32_t)TILE, n - tile_base);
 
-        // (1) take the next ticket and prefetch that tile into the other buffer
-        if (tid == 0) {
-            uint32_t t = atomicAdd(ticket, 1u);
-            s.next_tile[buf ^ 1] = t;
-            if (use_tma && t < ntiles) {
-                fence_proxy_async();  // last iteration's generic stores to keys[buf^1] come first
-                issue_load(t, buf ^ 1);
-            }
-        }
-#pragma unroll
-        for (int j = lane; j < RADIX; j += 32) s.warp_hist[warp][j] = 0;
-
-        // (2) keys -> registers, warp-striped so that tile order == rank order
+        // (1) keys -> registers, warp-striped so that tile order == rank order
         uint32_t key[KPT];
         const uint32_t wbase = warp * (KPT * 32) + lane;
         if (use_tma) {
-            mbar_wait(&s.mbar[buf], (it >> 1) & 1);
+            mbar_wait(&s.mbar, it & 1);
             if (valid == TILE) {
 #pragma unroll
-                for (int i = 0; i < KPT; i++) key[i] = s.keys[buf][wbase + i * 32];
+                for (int i = 0; i < KPT; i++) key[i] = s.keys[wbase + i * 32];
             } else {
                 const uint32_t staged = ((valid * 4u) & ~15u) >> 2;
 #pragma unroll
                 for (int i = 0; i < KPT; i++) {
                     const uint32_t idx = wbase + i * 32;
-                    key[i] = idx < staged ? s.keys[buf][idx] : (idx < valid ? in[(size_t)tile_base + idx] : 0xffffffffu);
+                    key[i] = idx < staged ? s.keys[idx] : (idx < valid ? in[(size_t)tile_base + idx] : 0xffffffffu);
                 }
             }
         } else {
@@ -370,78 +374,85 @@ __global__ void __launch_bounds__(THREADS, MINB)
                 key[i] = idx < valid ? in[(size_t)tile_base + idx] : 0xffffffffu;
             }
         }
-        __syncwarp();
+        __syncwarp();  // this warp's counters were zeroed by other lanes
 
-        // (3) early counts: per-warp digit histogram
+        // (2) early counts: per-warp digit histogram, in bytes
 #pragma unroll
-        for (int i = 0; i < KPT; i++) atomicAdd(&s.warp_hist[warp][binner.bin(key[i])], 1u);
+        for (int i = 0; i < KPT; i++) atomicAdd(reinterpret_cast<uint32_t *>(my_hist + binner.bin4(key[i])), 4u);
         __syncthreads();
 
-        // (4) bin threads: reduce over warps, publish the tile aggregate,
+        // (3) bin threads: reduce over warps, publish the tile aggregate,
         //     scan bins, turn warp counters into running offsets in the tile
-        uint32_t my_count = 0, my_start = 0;
+        uint32_t my_count = 0, my_start4 = 0, padded4 = 0;
         if (tid < RADIX) {
 #pragma unroll
-            for (int w = 0; w < NWARPS; w++) my_count += s.warp_hist[w][tid];
-            uint32_t agg = my_count;
-            if ((uint32_t)tid == pad_bin) agg -= (uint32_t)TILE - valid;  // padding keys carry the top digit
-            st_relaxed(&desc[(size_t)cur * RADIX + tid], (cur == 0 ? DESC_INCL : DESC_AGG) | agg);
-            my_count = agg | 0u;  // keep the unpadded count for the look-back
+            for (int w = 0; w < NWARPS; w++) padded4 += s.warp_hist[w][tid];
+            my_count = padded4 >> 2;
+            if ((uint32_t)tid == pad_bin) my_count -= (uint32_t)TILE - valid;  // padding keys carry the top digit
+            st_relaxed(&desc[(size_t)cur * RADIX + tid], (cur == 0 ? DESC_INCL : DESC_AGG) | my_count);
         }
-        {
-            uint32_t padded = 0;
-            if (tid < RADIX) {
-                padded = my_count;
-                if ((uint32_t)tid == pad_bin) padded += (uint32_t)TILE - valid;
-            }
-            my_start = block_excl_scan_256(padded, s.s_warp, nullptr);
-        }
+        // first look-back loads go out now and land while the tile is ranked
+        uint32_t lbv[LB];
         if (tid < RADIX) {
-            uint32_t run = my_start;
+#pragma unroll
+            for (int k = 0; k < LB; k++)
+                lbv[k] = (uint32_t)k < cur ? ld_relaxed(&desc[(size_t)(cur - 1 - k) * RADIX + tid]) : DESC_INCL;
+        }
+        my_start4 = block_excl_scan_256(padded4, s.s_warp, nullptr);
+        if (tid < RADIX) {
+            uint32_t run = my_start4;
 #pragma unroll
             for (int w = 0; w < NWARPS; w++) {
-                uint32_t c = s.warp_hist[w][tid];
+                const uint32_t c = s.warp_hist[w][tid];
                 s.warp_hist[w][tid] = run;
                 run += c;
             }
         }
         __syncthreads();
 
-        // (5) rank: position of every key in the digit-sorted tile
-        uint32_t pos[KPT];
-        const uint32_t my_hist = smem_u32(&s.warp_hist[warp][0]);
-#if defined(SORT_EXPERIMENT_RANK_ATOMS)
-        // EXPERIMENT ONLY (never the shipped default): rank straight from the returning
-        // shared atomic, relying on the hardware serving colliding lanes in lane order.
+        // (4) rank every key and move it to its place in the digit-sorted tile
+        //     (all warps hold their keys in registers since (2), so the landing
+        //     buffer can be overwritten)
+        if (RANK == RANK_ATOMS) {
 #pragma unroll
-        for (int i = 0; i < KPT; i++) {
-            pos[i] = atomicAdd(&s.warp_hist[warp][binner.bin(key[i])], 1u);
-            __syncwarp();
+            for (int i = 0; i < KPT; i++) {
+                const uint32_t p4 = atomicAdd(reinterpret_cast<uint32_t *>(my_hist + binner.bin4(key[i])), 4u);
+                *reinterpret_cast<uint32_t *>(tile_bytes + p4) = key[i];
+            }
+        } else {
+            const uint32_t lt = lanemask_lt();
+            const int nbits = binner.nbits();
+            const uint32_t hist_addr = smem_u32(my_hist);
+#pragma unroll
+            for (int i = 0; i < KPT; i++) {
+                const uint32_t d4 = binner.bin4(key[i]);
+                const uint32_t peers = match_digit<NBITS>(d4 >> 2, nbits);
+                const uint32_t before = __popc(peers & lt);
+                const int top = 31 - __clz(peers);  // highest peer lane leads; its `before` + 1 is the group size
+                uint32_t off4 = leader_atom_add(hist_addr + d4, (before + 1u) * 4u, lane == top);
+                off4 = __shfl_sync(0xffffffffu, off4, top);
+                *reinterpret_cast<uint32_t *>(tile_bytes + off4 + before * 4u) = key[i];
+            }
         }
-        (void)lt; (void)my_hist; (void)nbits;
-#else
-#pragma unroll
-        for (int i = 0; i < KPT; i++) {
-            const uint32_t d = binner.bin(key[i]);
-            const uint32_t peers = match_digit<NBITS>(d, nbits);
-            const uint32_t before = __popc(peers & lt);
-            const int top = 31 - __clz(peers);  // highest peer lane leads; its `before` + 1 is the group size
-            uint32_t off = leader_atom_add(my_hist + d * 4u, before + 1u, lane == top);
-            off = __shfl_sync(0xffffffffu, off, top);
-            pos[i] = off + before;
-        }
-#endif
-        // every warp has its keys in registers since (3); the staging buffer can be overwritten
-#pragma unroll
-        for (int i = 0; i < KPT; i++) s.keys[buf][pos[i]] = key[i];
 
-        // (6) decoupled look-back for this thread's bin
+        // (5) decoupled look-back for this thread's bin
         if (tid < RADIX) {
             uint32_t excl = 0;
             if (cur != 0) {
                 uint32_t j = cur - 1;
-                while (true) {
-                    uint32_t v = ld_relaxed(&desc[(size_t)j * RADIX + tid]);
+                bool done = false;
+#pragma unroll
+                for (int k = 0; k < LB; k++) {
+                    if (!done) {
+                        uint32_t v = lbv[k];
+                        while ((v >> 30) == 0) v = ld_relaxed(&desc[(size_t)j * RADIX + tid]);
+                        excl += v & DESC_VAL;
+                        if (v & DESC_INCL) done = true;
+                        else --j;
+                    }
+                }
+                while (!done) {
+                    const uint32_t v = ld_relaxed(&desc[(size_t)j * RADIX + tid]);
                     if ((v >> 30) == 0) continue;
                     excl += v & DESC_VAL;
                     if (v & DESC_INCL) break;
@@ -449,23 +460,33 @@ __global__ void __launch_bounds__(THREADS, MINB)
                 }
                 st_relaxed(&desc[(size_t)cur * RADIX + tid], DESC_INCL | (excl + my_count));
             }
+            const uint32_t my_start = my_start4 >> 2;
             if (PTR_OUT) {
                 const unsigned long long gptr = static_cast<const unsigned long long *>(base_v)[tid];
-                s.tile_ptr[tid] = gptr + 4ull * (unsigned long long)excl - 4ull * (unsigned long long)my_start;
+                s.tile_dst[tid] = gptr + 4ull * (unsigned long long)excl - 4ull * (unsigned long long)my_start;
             } else {
                 const uint32_t gbase = static_cast<const uint32_t *>(base_v)[tid];
-                s.tile_offs[tid] = gbase + excl - my_start;
+                s.tile_dst[tid] = gbase + excl - my_start;
                 if (base_next && cur == ntiles - 1) base_next[tid] = gbase + excl + my_count;
             }
         }
+        // the counters are dead until the next tile's (2): clear this warp's own
+#pragma unroll
+        for (int j = lane; j < RADIX; j += 32) s.warp_hist[warp][j] = 0;
+        uint32_t t_next = 0;
+        if (tid == 0) t_next = atomicAdd(ticket, 1u);  // in flight during the write-out
         __syncthreads();
 
-        // (7) coalesced write-out: consecutive threads, consecutive sorted keys
+        // (6) coalesced write-out: consecutive threads, consecutive sorted keys
         auto put = [&](uint32_t p) {
-            const uint32_t k = s.keys[buf][p];
-            const uint32_t d = binner.bin(k);
-            if (PTR_OUT) *reinterpret_cast<uint32_t *>(s.tile_ptr[d] + 4ull * p) = k;
-            else out[s.tile_offs[d] + p] = k;
+            const uint32_t k = s.keys[p];
+            const uint32_t d4 = binner.bin4(k);
+            if (PTR_OUT)
+                *reinterpret_cast<uint32_t *>(*reinterpret_cast<const unsigned long long *>(
+                                                  reinterpret_cast<const unsigned char *>(s.tile_dst) + 2 * d4) +
+                                              4ull * p) = k;
+            else
+                out[*reinterpret_cast<const uint32_t *>(reinterpret_cast<const unsigned char *>(s.tile_dst) + d4) + p] = k;
         };
         if (valid == TILE) {
 #pragma unroll
@@ -473,9 +494,42 @@ __global__ void __launch_bounds__(THREADS, MINB)
         } else {
             for (uint32_t p = tid; p < valid; p += THREADS) put(p);
         }
-        __syncthreads();
-        cur = s.next_tile[buf ^ 1];
+        if (tid == 0) s.next_tile = t_next;
+        __syncthreads();  // the tile buffer is free again
+        cur = s.next_tile;
+        if (tid == 0 && use_tma && cur < ntiles) {
+            fence_proxy_async();  // generic-proxy accesses to keys[] come before the bulk copy's writes
+            issue_load(cur);
+        }
     }
+}
+
+// Device self-test behind LIBSORT_RANK=auto (engine.cu choose_rank_mode): every
+// lane adds to a pseudo-random counter of its warp and gets the old value; the
+// lanes of one instruction that named the same counter must have been served
+// in ascending lane order.  out[0] += violations, out[1] += colliding lanes seen.
+__global__ void __launch_bounds__(1024) k_selftest_atoms_order(unsigned long long *out, int iters)
+{
+    __shared__ uint32_t h[32][RADIX];
+    for (int i = threadIdx.x; i < 32 * RADIX; i += blockDim.x) (&h[0][0])[i] = 0;
+    __syncthreads();
+    uint32_t *my = h[threadIdx.x >> 5];
+    const uint32_t lane = threadIdx.x & 31, lt = lanemask_lt();
+    uint32_t s = (threadIdx.x + 1) * 2654435761u + blockIdx.x * 97u;
+    uint32_t bad = 0, seen = 0;
+    for (int i = 0; i < iters; i++) {
+        s = s * 1664525u + 1013904223u;
+        uint32_t d = s >> 24;
+        if ((i & 3) == 1) d &= 15;               // denser collisions
+        if ((i & 3) == 3) d = (lane * 5 + i) & 1;  // two 16-lane pile-ups
+        const uint32_t r = atomicAdd(&my[d], 1u);
+        const uint32_t peers = match_digit<8>(d, 8);
+        const uint32_t r0 = __shfl_sync(0xffffffffu, r, __ffs(peers) - 1);
+        if (r != r0 + __popc(peers & lt)) bad++;
+        seen += (peers & lt) ? 1 : 0;
+    }
+    if (bad) atomicAdd(&out[0], (unsigned long long)bad);
+    atomicAdd(&out[1], (unsigned long long)seen);
 }
 
 // ------------------------------------------------------- distributed sort --
