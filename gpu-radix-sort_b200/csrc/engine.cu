@@ -22,7 +22,7 @@ namespace b200sort {
 #define SORT_MINB 4
 #endif
 #ifndef SORT_LB
-#define SORT_LB 2   // look-back descriptors fetched ahead of the ranking phase
+#define SORT_LB 4   // look-back descriptors fetched ahead of the ranking phase
 #endif
 #ifndef HIST_THREADS
 #define HIST_THREADS 512

@@ -439,24 +439,25 @@ __global__ void __launch_bounds__(THREADS, MINB)
         if (tid < RADIX) {
             uint32_t excl = 0;
             if (cur != 0) {
-                uint32_t j = cur - 1;
+                // walk back LB predecessors per round trip: the loads of a window are
+                // in flight together; an unpublished descriptor restarts the window there
+                uint32_t j = cur - 1;  // next predecessor to account for
                 bool done = false;
+                while (true) {
 #pragma unroll
-                for (int k = 0; k < LB; k++) {
-                    if (!done) {
-                        uint32_t v = lbv[k];
-                        while ((v >> 30) == 0) v = ld_relaxed(&desc[(size_t)j * RADIX + tid]);
-                        excl += v & DESC_VAL;
-                        if (v & DESC_INCL) done = true;
-                        else --j;
+                    for (int k = 0; k < LB; k++) {
+                        if (!done) {
+                            const uint32_t v = lbv[k];
+                            if ((v >> 30) == 0) break;
+                            excl += v & DESC_VAL;
+                            if (v & DESC_INCL) done = true;
+                            else --j;
+                        }
                     }
-                }
-                while (!done) {
-                    const uint32_t v = ld_relaxed(&desc[(size_t)j * RADIX + tid]);
-                    if ((v >> 30) == 0) continue;
-                    excl += v & DESC_VAL;
-                    if (v & DESC_INCL) break;
-                    --j;
+                    if (done) break;
+#pragma unroll
+                    for (int k = 0; k < LB; k++)
+                        lbv[k] = (uint32_t)k <= j ? ld_relaxed(&desc[(size_t)(j - k) * RADIX + tid]) : DESC_INCL;
                 }
                 st_relaxed(&desc[(size_t)cur * RADIX + tid], DESC_INCL | (excl + my_count));
             }
