@@ -16,10 +16,10 @@ namespace b200sort {
 #define SORT_THREADS 256
 #endif
 #ifndef SORT_KPT
-#define SORT_KPT 32
+#define SORT_KPT 56
 #endif
 #ifndef SORT_MINB
-#define SORT_MINB 4
+#define SORT_MINB 3
 #endif
 #ifndef SORT_LB
 #define SORT_LB 4   // look-back descriptors fetched ahead of the ranking phase
