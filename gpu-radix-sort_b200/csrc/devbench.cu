@@ -3,6 +3,7 @@
 //   devbench check            parity sweep vs. a host stable counting sort
 //   devbench time N [reps]    full sort + 8/16-bit partial timings at N keys
 #include <algorithm>
+#include <cmath>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -128,12 +129,17 @@ static int run_check()
     return fails ? 1 : 0;
 }
 
-static int run_time(size_t n, int reps)
+static int run_time(size_t n, int reps, const char *dist)
 {
     Dev d;
     d.ensure(n);
     std::vector<uint32_t> h(n);
     populateInput(h.data(), n);
+    if (!strcmp(dist, "sorted")) std::sort(h.begin(), h.end());
+    else if (!strcmp(dist, "consthigh")) for (auto &k : h) k = 0xAB000000u | (k & 0xffffffu);
+    else if (!strcmp(dist, "zipf")) for (auto &k : h) k = (uint32_t)(exp2(32.0 * k / 4294967296.0)) - 1u;  // log-uniform
+    else if (!strcmp(dist, "allsame")) for (auto &k : h) k = 0x12345678u;
+    printf("-- input: %s\n", dist);
     CHECK(cudaMemcpy(d.in, h.data(), n * 4, cudaMemcpyHostToDevice));
     struct Cfg { uint32_t off, width; const char *name; double bytes_per_key; } cfgs[] = {
         {0, 32, "full32", 36}, {0, 8, "partial8", 12}, {0, 16, "partial16", 20}};
@@ -164,7 +170,7 @@ static int run_time(size_t n, int reps)
 int main(int argc, char **argv)
 {
     if (argc >= 2 && !strcmp(argv[1], "check")) return run_check();
-    if (argc >= 3 && !strcmp(argv[1], "time")) return run_time(strtoull(argv[2], 0, 0), argc >= 4 ? atoi(argv[3]) : 10);
-    fprintf(stderr, "usage: devbench check | time N [reps]\n");
+    if (argc >= 3 && !strcmp(argv[1], "time")) return run_time(strtoull(argv[2], 0, 0), argc >= 4 ? atoi(argv[3]) : 10, argc >= 5 ? argv[4] : "uniform");
+    fprintf(stderr, "usage: devbench check | time N [reps] [uniform|sorted|consthigh|zipf|allsame]\n");
     return 2;
 }

@@ -12,6 +12,10 @@
 namespace b200sort {
 
 // ---- compiled-in kernel variant -------------------------------------------
+// Two tile shapes.  A: the atomic-ranking scatter (few registers per key, big
+// tiles).  B: the ballot-ranking kernels -- the fallback for devices that fail the
+// lane-order self-test, and the <= 16-way splitter scatter of the distributed sort,
+// whose few bins would serialise atomic ranking.
 #ifndef SORT_THREADS
 #define SORT_THREADS 256
 #endif
@@ -22,7 +26,13 @@ namespace b200sort {
 #define SORT_MINB 3
 #endif
 #ifndef SORT_LB
-#define SORT_LB 4   // look-back descriptors fetched ahead of the ranking phase
+#define SORT_LB 4   // look-back descriptors fetched per round trip
+#endif
+#ifndef BALLOT_KPT
+#define BALLOT_KPT 32
+#endif
+#ifndef BALLOT_MINB
+#define BALLOT_MINB 4
 #endif
 #ifndef HIST_THREADS
 #define HIST_THREADS 512
@@ -31,15 +41,18 @@ namespace b200sort {
 #define HIST_REPL 2
 #endif
 
-constexpr int kTile = SORT_THREADS * SORT_KPT;
-using SortSmem = OnesweepSmem<SORT_THREADS, SORT_KPT, false>;
-using SortSmemPtr = OnesweepSmem<SORT_THREADS, SORT_KPT, true>;
+constexpr int kTileA = SORT_THREADS * SORT_KPT;
+constexpr int kTileB = SORT_THREADS * BALLOT_KPT;
+constexpr int kTileMin = kTileA < kTileB ? kTileA : kTileB;
+using SmemA = OnesweepSmem<SORT_THREADS, SORT_KPT, false, RadixBinner::Arg>;
+using SmemB = OnesweepSmem<SORT_THREADS, BALLOT_KPT, false, RadixBinner::Arg>;
+using SmemSplit = OnesweepSmem<SORT_THREADS, BALLOT_KPT, true, SplitBinner::Arg>;
 
-template <int RANK, int NBITS, class Binner, bool PTR_OUT>
-using SortKernel = decltype(&k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, RANK, NBITS, SORT_LB, Binner, PTR_OUT>);
-#define SORT_KERNEL(RANK, NBITS, BINNER, PTR) k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, RANK, NBITS, SORT_LB, BINNER, PTR>
+#define KERNEL_A(NBITS) k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, RANK_ATOMS, NBITS, SORT_LB, RadixBinner, false>
+#define KERNEL_B(NBITS) k_onesweep<SORT_THREADS, BALLOT_KPT, BALLOT_MINB, RANK_BALLOT, NBITS, SORT_LB, RadixBinner, false>
+#define KERNEL_SPLIT k_onesweep<SORT_THREADS, BALLOT_KPT, BALLOT_MINB, RANK_BALLOT, 0, SORT_LB, SplitBinner, true>
 
-int tile_keys() { return kTile; }
+int tile_keys() { return kTileA; }
 
 // workspace layout, in uint32 words
 constexpr size_t WS_HIST = 0;                                   // [4][256]
@@ -51,24 +64,24 @@ constexpr int MAX_PORTIONS = 8;
 static std::atomic<uint32_t> g_portion_tiles{0};
 void debug_set_portion_tiles(uint32_t tiles) { g_portion_tiles.store(tiles); }
 
-static uint32_t portion_tiles()
+static uint32_t portion_tiles(int tile)
 {
     uint32_t t = g_portion_tiles.load();
-    return t ? t : (uint32_t)(((1u << 30) - 1) / kTile);
+    return t ? t : (uint32_t)(((1u << 30) - 1) / tile);
 }
 
-static size_t num_tiles(size_t n) { return (n + kTile - 1) / kTile; }
+static size_t num_tiles(size_t n, int tile) { return (n + tile - 1) / tile; }
 
 size_t workspace_bytes(size_t n)
 {
-    return (WS_DESC + (size_t)MAX_PASSES * num_tiles(n) * RADIX) * sizeof(uint32_t);
+    return (WS_DESC + (size_t)MAX_PASSES * num_tiles(n, kTileMin) * RADIX) * sizeof(uint32_t);
 }
 
 // ---- per-device launch parameters -----------------------------------------
 struct DevInfo {
     bool ready = false;
     int sms = 0;
-    int sort_occ = 0;
+    int occ_a = 0, occ_b = 0, occ_split = 0;  // resident CTAs per SM of the three scatter kernels
     int hist_occ = 0;
     bool rank_atoms = false;  // rank keys with returning shared atomics (self-tested) instead of ballots
 };
@@ -157,30 +170,31 @@ static cudaError_t dev_info(DevInfo **out)
     if (!d.ready) {
         e = cudaDeviceGetAttribute(&d.sms, cudaDevAttrMultiProcessorCount, dev);
         if (e != cudaSuccess) return e;
-        auto kern = SORT_KERNEL(RANK_ATOMS, 0, RadixBinner, false);
-        const int sm = (int)sizeof(SortSmem), smp = (int)sizeof(SortSmemPtr);
-        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+        struct { const void *fn; int smem; } kernels[] = {
+            {(const void *)KERNEL_A(8), (int)sizeof(SmemA)},     {(const void *)KERNEL_A(0), (int)sizeof(SmemA)},
+            {(const void *)KERNEL_B(8), (int)sizeof(SmemB)},     {(const void *)KERNEL_B(0), (int)sizeof(SmemB)},
+            {(const void *)KERNEL_SPLIT, (int)sizeof(SmemSplit)}};
+        for (auto &k : kernels) {
+            e = cudaFuncSetAttribute(k.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, k.smem);
+            if (e != cudaSuccess) return e;
+        }
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.occ_a, KERNEL_A(8), SORT_THREADS, sizeof(SmemA));
         if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(SORT_KERNEL(RANK_BALLOT, 8, RadixBinner, false), cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.occ_b, KERNEL_B(8), SORT_THREADS, sizeof(SmemB));
         if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(SORT_KERNEL(RANK_BALLOT, 0, RadixBinner, false), cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
-        if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(SORT_KERNEL(RANK_ATOMS, 0, SplitBinner, true), cudaFuncAttributeMaxDynamicSharedMemorySize, smp);
-        if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(SORT_KERNEL(RANK_BALLOT, 0, SplitBinner, true), cudaFuncAttributeMaxDynamicSharedMemorySize, smp);
-        if (e != cudaSuccess) return e;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.sort_occ, kern, SORT_THREADS, sizeof(SortSmem));
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.occ_split, KERNEL_SPLIT, SORT_THREADS, sizeof(SmemSplit));
         if (e != cudaSuccess) return e;
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.hist_occ, k_histogram<4, HIST_THREADS, HIST_REPL>,
                                                           HIST_THREADS, 0);
         if (e != cudaSuccess) return e;
-        if (d.sort_occ < 1 || d.hist_occ < 1) return cudaErrorLaunchOutOfResources;
+        if (d.occ_a < 1 || d.occ_b < 1 || d.occ_split < 1 || d.hist_occ < 1) return cudaErrorLaunchOutOfResources;
         e = choose_rank_mode(dev, &d.rank_atoms);
         if (e != cudaSuccess) return e;
         if (const char *dbg = getenv("LIBSORT_DEBUG"))
             if (dbg[0] == '1')
-                fprintf(stderr, "libsort: dev %d sms=%d tile=%d sort_occ=%d hist_occ=%d smem=%zu rank=%s\n", dev, d.sms, kTile,
-                        d.sort_occ, d.hist_occ, sizeof(SortSmem), d.rank_atoms ? "atoms" : "ballot");
+                fprintf(stderr, "libsort: dev %d sms=%d rank=%s tiles A/B=%d/%d occ A/B/split=%d/%d/%d hist_occ=%d smem A/B=%zu/%zu\n", dev,
+                        d.sms, d.rank_atoms ? "atoms" : "ballot", kTileA, kTileB, d.occ_a, d.occ_b, d.occ_split, d.hist_occ,
+                        sizeof(SmemA), sizeof(SmemB));
         d.ready = true;
     }
     *out = &d;
@@ -285,8 +299,9 @@ cudaError_t sort_bits(const uint32_t *in, uint32_t *a, uint32_t *b, uint32_t *wa
     CK(dev_info(&dev));
     uint32_t *ws = static_cast<uint32_t *>(workspace);
     uint32_t *ghist = ws + WS_HIST, *base = ws + WS_BASE, *tickets = ws + WS_TICKET, *desc = ws + WS_DESC;
-    const size_t ntiles = num_tiles(n);
-    const uint32_t ptiles = portion_tiles();
+    const int tile = dev->rank_atoms ? kTileA : kTileB;
+    const size_t ntiles = num_tiles(n, tile);
+    const uint32_t ptiles = portion_tiles(tile);
     const size_t nportions = (ntiles + ptiles - 1) / ptiles;
     if (nportions > MAX_PORTIONS) return cudaErrorInvalidValue;
 
@@ -325,15 +340,15 @@ cudaError_t sort_bits(const uint32_t *in, uint32_t *a, uint32_t *b, uint32_t *wa
         const int use_tma = aligned && ((reinterpret_cast<uintptr_t>(src) & 15u) == 0);
         for (size_t q = 0; q < nportions; q++) {
             const size_t t0 = q * ptiles, t1 = std::min(ntiles, t0 + ptiles);
-            const size_t k0 = t0 * kTile, k1 = std::min(n, t1 * (size_t)kTile);
+            const size_t k0 = t0 * tile, k1 = std::min(n, t1 * (size_t)tile);
             const uint32_t nt = (uint32_t)(t1 - t0);
-            const int grid = (int)std::min<size_t>(nt, (size_t)dev->sms * dev->sort_occ);
+            const int grid = (int)std::min<size_t>(nt, (size_t)dev->sms * (dev->rank_atoms ? dev->occ_a : dev->occ_b));
             uint32_t *bcur = base + ((q & 1) * MAX_PASSES + p) * RADIX;
             uint32_t *bnext = (q + 1 < nportions) ? base + (((q + 1) & 1) * MAX_PASSES + p) * RADIX : nullptr;
-            auto kern = dev->rank_atoms          ? SORT_KERNEL(RANK_ATOMS, 0, RadixBinner, false)
-                        : plan.mask[p] == 0xffu ? SORT_KERNEL(RANK_BALLOT, 8, RadixBinner, false)
-                                                : SORT_KERNEL(RANK_BALLOT, 0, RadixBinner, false);
-            kern<<<grid, SORT_THREADS, sizeof(SortSmem), st>>>(
+            const bool full_digit = plan.mask[p] == 0xffu;
+            auto kern = dev->rank_atoms ? (full_digit ? KERNEL_A(8) : KERNEL_A(0)) : (full_digit ? KERNEL_B(8) : KERNEL_B(0));
+            const size_t smem = dev->rank_atoms ? sizeof(SmemA) : sizeof(SmemB);
+            kern<<<grid, SORT_THREADS, smem, st>>>(
                 src + k0, dst, (uint32_t)(k1 - k0), RadixBinner::Arg{plan.shift[p], plan.mask[p]}, bcur, bnext,
                 desc + ((size_t)p * ntiles + t0) * RADIX, tickets + p * MAX_PORTIONS + q, nt, use_tma);
             launches++;
@@ -413,17 +428,16 @@ cudaError_t scatter_by_splitters(const uint32_t *in, size_t n, const uint32_t *s
     DevInfo *dev = nullptr;
     CK(dev_info(&dev));
     uint32_t *ws = static_cast<uint32_t *>(workspace);
-    const size_t ntiles = num_tiles(n);
+    const size_t ntiles = num_tiles(n, kTileB);
     CK(cudaMemsetAsync(ws, 0, (WS_DESC + ntiles * RADIX) * sizeof(uint32_t), st));
     PtrTable t{};
     for (int i = 0; i <= nsplit; i++) t.p[i] = dest_ptrs[i];
     unsigned long long *d_ptrs = reinterpret_cast<unsigned long long *>(ws + WS_HIST);
     k_store_ptrs<<<1, 32, 0, st>>>(t, d_ptrs);
-    const int grid = (int)std::min<size_t>(ntiles, (size_t)dev->sms * dev->sort_occ);
+    const int grid = (int)std::min<size_t>(ntiles, (size_t)dev->sms * dev->occ_split);
     const int use_tma = (reinterpret_cast<uintptr_t>(in) & 15u) == 0;
-    auto kern = dev->rank_atoms ? SORT_KERNEL(RANK_ATOMS, 0, SplitBinner, true) : SORT_KERNEL(RANK_BALLOT, 0, SplitBinner, true);
-    kern<<<grid, SORT_THREADS, sizeof(SortSmemPtr), st>>>(in, nullptr, (uint32_t)n, SplitBinner::Arg{splitters, nsplit}, d_ptrs,
-                                                          nullptr, ws + WS_DESC, ws + WS_TICKET, (uint32_t)ntiles, use_tma);
+    KERNEL_SPLIT<<<grid, SORT_THREADS, sizeof(SmemSplit), st>>>(in, nullptr, (uint32_t)n, SplitBinner::Arg{splitters, nsplit}, d_ptrs,
+                                                                nullptr, ws + WS_DESC, ws + WS_TICKET, (uint32_t)ntiles, use_tma);
     return cudaGetLastError();
 }
 

@@ -194,18 +194,9 @@ __global__ void __launch_bounds__(256) k_scan_hist(const uint32_t *__restrict__ 
 // instructions (LOP3 -> predicate, VOTE, SEL, LOP3): peers &= ballot(bit) ^ (bit ? 0 : ~0).
 __device__ __forceinline__ uint32_t match_bit(uint32_t peers, uint32_t d, uint32_t bitmask)
 {
-    asm("{\n\t"
-        ".reg .pred p;\n\t"
-        ".reg .b32 t, m, x;\n\t"
-        "and.b32 t, %1, %2;\n\t"
-        "setp.ne.u32 p, t, 0;\n\t"
-        "vote.sync.ballot.b32 m, p, 0xffffffff;\n\t"
-        "selp.b32 x, 0, -1, p;\n\t"
-        "lop3.b32 %0, %0, m, x, 0x60;\n\t"
-        "}"
-        : "+r"(peers)
-        : "r"(d), "r"(bitmask));
-    return peers;
+    const bool bit = (d & bitmask) != 0;
+    const uint32_t m = __ballot_sync(0xffffffffu, bit);
+    return peers & (m ^ (bit ? 0u : 0xffffffffu));
 }
 
 template <int NBITS>
@@ -274,8 +265,40 @@ struct SplitBinner {
     __device__ __forceinline__ int nbits() const { return 32 - __clz(nsplit); }  // bins 0..nsplit
 };
 
-template <int THREADS, int KPT, bool PTR_OUT>
+// Out-of-line ranking for a tile dominated by one digit (cold path of the
+// atomic-ranking kernel; keys come through local memory so that the hot path keeps
+// its registers).  The hardware serialises the lanes of a row that add to the same
+// counter, so the lanes holding the dominant digit hd4/4 are ranked with one ballot
+// and a single atomic by their highest lane; all other lanes use their own atomic.
+template <class Binner, class Smem>
+__device__ __noinline__ void rank_tile_heavy(const uint32_t *keys, Smem *sp)
+{
+    Smem &s = *sp;
+    const Binner binner(s.binner_arg);
+    const uint32_t hd4 = s.heavy_d4;
+    unsigned char *const my_hist = reinterpret_cast<unsigned char *>(s.warp_hist[threadIdx.x >> 5]);
+    unsigned char *const tile_bytes = reinterpret_cast<unsigned char *>(s.keys);
+    const uint32_t lt = lanemask_lt();
+    const int lane = threadIdx.x & 31;
+#pragma unroll 4
+    for (int i = 0; i < Smem::KEYS_PER_THREAD; i++) {
+        const uint32_t k = keys[i];
+        const uint32_t d4 = binner.bin4(k);
+        const bool is = d4 == hd4;
+        const uint32_t m = __ballot_sync(0xffffffffu, is);  // warp-uniform
+        const int top = 31 - __clz(m | 1u);
+        const uint32_t before4 = __popc(m & lt) * 4u;
+        uint32_t p4 = 0;
+        if (!is || lane == top) p4 = atomicAdd(reinterpret_cast<uint32_t *>(my_hist + d4), is ? before4 + 4u : 4u);
+        const uint32_t g4 = __shfl_sync(0xffffffffu, p4, top);
+        if (is) p4 = g4 + before4;
+        *reinterpret_cast<uint32_t *>(tile_bytes + p4) = k;
+    }
+}
+
+template <int THREADS, int KPT, bool PTR_OUT, class BinnerArg>
 struct OnesweepSmem {
+    static constexpr int KEYS_PER_THREAD = KPT;
     static constexpr int TILE = THREADS * KPT;
     static constexpr int NWARPS = THREADS / 32;
     alignas(128) uint32_t keys[TILE];          // TMA landing buffer, then the digit-sorted tile
@@ -286,6 +309,8 @@ struct OnesweepSmem {
     uint32_t s_warp[8];
     alignas(8) uint64_t mbar;
     uint32_t next_tile;
+    BinnerArg binner_arg;  // copy for the out-of-line heavy-tile path
+    uint32_t heavy_d4;  // 4 * (a digit holding more than a quarter of the current tile), valid when the tile votes heavy
 };
 
 constexpr int RANK_BALLOT = 0;  // one vote.ballot per digit bit + a leader atomic: architecturally ordered
@@ -308,7 +333,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
                const void *__restrict__ base_v, uint32_t *__restrict__ base_next, uint32_t *__restrict__ desc,
                uint32_t *__restrict__ ticket, uint32_t ntiles, int use_tma)
 {
-    using Smem = OnesweepSmem<THREADS, KPT, PTR_OUT>;
+    using Smem = OnesweepSmem<THREADS, KPT, PTR_OUT, typename Binner::Arg>;
     constexpr int TILE = Smem::TILE;
     constexpr int NWARPS = Smem::NWARPS;
     static_assert(THREADS >= RADIX, "need one thread per bin");
@@ -340,6 +365,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
         fence_mbar_init();
         const uint32_t t = atomicAdd(ticket, 1u);
         s.next_tile = t;
+        s.binner_arg = binner_arg;
         if (use_tma && t < ntiles) issue_load(t);
     }
 #pragma unroll
@@ -376,9 +402,11 @@ __global__ void __launch_bounds__(THREADS, MINB)
         }
         __syncwarp();  // this warp's counters were zeroed by other lanes
 
-        // (2) early counts: per-warp digit histogram, in bytes
+        // (2) early counts: per-warp digit histogram (adding 1 lets same-digit lanes be merged)
 #pragma unroll
-        for (int i = 0; i < KPT; i++) atomicAdd(reinterpret_cast<uint32_t *>(my_hist + binner.bin4(key[i])), 4u);
+        //     (indexed with bin(), not bin4(): a different expression than (4) uses, so that the
+        //     optimiser recomputes the address there instead of spilling KPT of them across barriers)
+        for (int i = 0; i < KPT; i++) atomicAdd(&s.warp_hist[warp][binner.bin(key[i])], 1u);
         __syncthreads();
 
         // (3) bin threads: reduce over warps, publish the tile aggregate,
@@ -387,7 +415,8 @@ __global__ void __launch_bounds__(THREADS, MINB)
         if (tid < RADIX) {
 #pragma unroll
             for (int w = 0; w < NWARPS; w++) padded4 += s.warp_hist[w][tid];
-            my_count = padded4 >> 2;
+            my_count = padded4;
+            padded4 <<= 2;  // bytes from here on
             if ((uint32_t)tid == pad_bin) my_count -= (uint32_t)TILE - valid;  // padding keys carry the top digit
             st_relaxed(&desc[(size_t)cur * RADIX + tid], (cur == 0 ? DESC_INCL : DESC_AGG) | my_count);
         }
@@ -405,19 +434,30 @@ __global__ void __launch_bounds__(THREADS, MINB)
             for (int w = 0; w < NWARPS; w++) {
                 const uint32_t c = s.warp_hist[w][tid];
                 s.warp_hist[w][tid] = run;
-                run += c;
+                run += c << 2;
             }
         }
-        __syncthreads();
+        // barrier + vote: does one digit hold more than a quarter of the tile?  (padded4 counts bytes)
+        const bool is_heavy = RANK == RANK_ATOMS && padded4 > (uint32_t)TILE;
+        if (is_heavy) s.heavy_d4 = (uint32_t)tid * 4u;  // up to three candidates: any one will do
+        const int heavy = __syncthreads_or(is_heavy);
 
         // (4) rank every key and move it to its place in the digit-sorted tile
         //     (all warps hold their keys in registers since (2), so the landing
         //     buffer can be overwritten)
         if (RANK == RANK_ATOMS) {
+            if (!heavy) {
 #pragma unroll
-            for (int i = 0; i < KPT; i++) {
-                const uint32_t p4 = atomicAdd(reinterpret_cast<uint32_t *>(my_hist + binner.bin4(key[i])), 4u);
-                *reinterpret_cast<uint32_t *>(tile_bytes + p4) = key[i];
+                for (int i = 0; i < KPT; i++) {
+                    const uint32_t p4 = atomicAdd(reinterpret_cast<uint32_t *>(my_hist + binner.bin4(key[i])), 4u);
+                    *reinterpret_cast<uint32_t *>(tile_bytes + p4) = key[i];
+                }
+            } else {
+                // one digit dominates the tile (skewed input): out-of-line path, see rank_tile_heavy
+                uint32_t spilled[KPT];
+#pragma unroll
+                for (int i = 0; i < KPT; i++) spilled[i] = key[i];
+                rank_tile_heavy<Binner, Smem>(spilled, &s);
             }
         } else {
             const uint32_t lt = lanemask_lt();
