@@ -34,6 +34,9 @@ namespace b200sort {
 #ifndef BALLOT_MINB
 #define BALLOT_MINB 4
 #endif
+#ifndef SPLIT_MINB
+#define SPLIT_MINB 3   // the splitter scatter keeps up to 15 splitters in registers
+#endif
 #ifndef HIST_THREADS
 #define HIST_THREADS 512
 #endif
@@ -46,11 +49,11 @@ constexpr int kTileB = SORT_THREADS * BALLOT_KPT;
 constexpr int kTileMin = kTileA < kTileB ? kTileA : kTileB;
 using SmemA = OnesweepSmem<SORT_THREADS, SORT_KPT, false, RadixBinner::Arg>;
 using SmemB = OnesweepSmem<SORT_THREADS, BALLOT_KPT, false, RadixBinner::Arg>;
-using SmemSplit = OnesweepSmem<SORT_THREADS, BALLOT_KPT, true, SplitBinner::Arg>;
+using SmemSplit = OnesweepSmem<SORT_THREADS, BALLOT_KPT, true, SplitArg>;
 
 #define KERNEL_A(NBITS) k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, RANK_ATOMS, NBITS, SORT_LB, RadixBinner, false>
 #define KERNEL_B(NBITS) k_onesweep<SORT_THREADS, BALLOT_KPT, BALLOT_MINB, RANK_BALLOT, NBITS, SORT_LB, RadixBinner, false>
-#define KERNEL_SPLIT k_onesweep<SORT_THREADS, BALLOT_KPT, BALLOT_MINB, RANK_BALLOT, 0, SORT_LB, SplitBinner, true>
+#define KERNEL_SPLIT(NS) k_onesweep<SORT_THREADS, BALLOT_KPT, SPLIT_MINB, RANK_BALLOT, 0, SORT_LB, SplitBinner<NS>, true>
 
 int tile_keys() { return kTileA; }
 
@@ -173,7 +176,8 @@ static cudaError_t dev_info(DevInfo **out)
         struct { const void *fn; int smem; } kernels[] = {
             {(const void *)KERNEL_A(8), (int)sizeof(SmemA)},     {(const void *)KERNEL_A(0), (int)sizeof(SmemA)},
             {(const void *)KERNEL_B(8), (int)sizeof(SmemB)},     {(const void *)KERNEL_B(0), (int)sizeof(SmemB)},
-            {(const void *)KERNEL_SPLIT, (int)sizeof(SmemSplit)}};
+            {(const void *)KERNEL_SPLIT(1), (int)sizeof(SmemSplit)},  {(const void *)KERNEL_SPLIT(3), (int)sizeof(SmemSplit)},
+            {(const void *)KERNEL_SPLIT(7), (int)sizeof(SmemSplit)},  {(const void *)KERNEL_SPLIT(15), (int)sizeof(SmemSplit)}};
         for (auto &k : kernels) {
             e = cudaFuncSetAttribute(k.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, k.smem);
             if (e != cudaSuccess) return e;
@@ -182,7 +186,7 @@ static cudaError_t dev_info(DevInfo **out)
         if (e != cudaSuccess) return e;
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.occ_b, KERNEL_B(8), SORT_THREADS, sizeof(SmemB));
         if (e != cudaSuccess) return e;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.occ_split, KERNEL_SPLIT, SORT_THREADS, sizeof(SmemSplit));
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.occ_split, KERNEL_SPLIT(15), SORT_THREADS, sizeof(SmemSplit));
         if (e != cudaSuccess) return e;
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.hist_occ, k_histogram<4, HIST_THREADS, HIST_REPL>,
                                                           HIST_THREADS, 0);
@@ -414,7 +418,11 @@ cudaError_t split_counts(const uint32_t *in, size_t n, const uint32_t *splitters
     if (n == 0) return cudaSuccess;
     const size_t want = (n / 4 + 4095) / 4096;
     const int grid = (int)std::max<size_t>(1, std::min<size_t>((size_t)dev->sms * 2, want));
-    k_dest_hist<<<grid, 1024, 0, st>>>(in, n, SplitBinner::Arg{splitters, nsplit}, d_counts);
+    const SplitArg arg{splitters, nsplit};
+    if (nsplit <= 1) k_dest_hist<1><<<grid, 1024, 0, st>>>(in, n, arg, d_counts);
+    else if (nsplit <= 3) k_dest_hist<3><<<grid, 1024, 0, st>>>(in, n, arg, d_counts);
+    else if (nsplit <= 7) k_dest_hist<7><<<grid, 1024, 0, st>>>(in, n, arg, d_counts);
+    else k_dest_hist<15><<<grid, 1024, 0, st>>>(in, n, arg, d_counts);
     return cudaGetLastError();
 }
 
@@ -436,8 +444,9 @@ cudaError_t scatter_by_splitters(const uint32_t *in, size_t n, const uint32_t *s
     k_store_ptrs<<<1, 32, 0, st>>>(t, d_ptrs);
     const int grid = (int)std::min<size_t>(ntiles, (size_t)dev->sms * dev->occ_split);
     const int use_tma = (reinterpret_cast<uintptr_t>(in) & 15u) == 0;
-    KERNEL_SPLIT<<<grid, SORT_THREADS, sizeof(SmemSplit), st>>>(in, nullptr, (uint32_t)n, SplitBinner::Arg{splitters, nsplit}, d_ptrs,
-                                                                nullptr, ws + WS_DESC, ws + WS_TICKET, (uint32_t)ntiles, use_tma);
+    auto kern = nsplit <= 1 ? KERNEL_SPLIT(1) : nsplit <= 3 ? KERNEL_SPLIT(3) : nsplit <= 7 ? KERNEL_SPLIT(7) : KERNEL_SPLIT(15);
+    kern<<<grid, SORT_THREADS, sizeof(SmemSplit), st>>>(in, nullptr, (uint32_t)n, SplitArg{splitters, nsplit}, d_ptrs, nullptr,
+                                                        ws + WS_DESC, ws + WS_TICKET, (uint32_t)ntiles, use_tma);
     return cudaGetLastError();
 }
 

@@ -244,20 +244,24 @@ struct RadixBinner {
     __device__ __forceinline__ int nbits() const { return __popc(mask); }
 };
 constexpr int MAX_SPLITTERS = 15;
+struct SplitArg { const uint32_t *d_splitters; int nsplit; };  // splitters live in device memory (no host round trip)
+// NS = compiled-in capacity (1, 3, 7 or 15 splitters for up to 2, 4, 8, 16 ranks):
+// only NS compares per key and NS registers.
+template <int NS>
 struct SplitBinner {
-    struct Arg { const uint32_t *d_splitters; int nsplit; };  // splitters live in device memory (no host round trip)
-    uint32_t v[MAX_SPLITTERS];
+    using Arg = SplitArg;
+    uint32_t v[NS];
     int nsplit;
     __device__ __forceinline__ explicit SplitBinner(const Arg &a) : nsplit(a.nsplit)
     {
 #pragma unroll
-        for (int j = 0; j < MAX_SPLITTERS; j++) v[j] = j < a.nsplit ? a.d_splitters[j] : 0xffffffffu;
+        for (int j = 0; j < NS; j++) v[j] = j < a.nsplit ? a.d_splitters[j] : 0xffffffffu;
     }
     __device__ __forceinline__ uint32_t bin(uint32_t key) const
     {
         uint32_t d = 0;
 #pragma unroll
-        for (int j = 0; j < MAX_SPLITTERS; j++) d += (j < nsplit && key >= v[j]) ? 1u : 0u;
+        for (int j = 0; j < NS; j++) d += (j < nsplit && key >= v[j]) ? 1u : 0u;
         return d;
     }
     __device__ __forceinline__ uint32_t bin4(uint32_t key) const { return bin(key) << 2; }
@@ -590,10 +594,11 @@ __global__ void k_sample(const uint32_t *__restrict__ in, uint32_t n, uint32_t *
 
 // Keys per destination rank (bank-private counters: lane l owns column l).
 struct PtrTable { unsigned long long p[MAX_SPLITTERS + 1]; };
-__global__ void __launch_bounds__(1024, 1) k_dest_hist(const uint32_t *__restrict__ in, size_t n, const SplitBinner::Arg arg,
+template <int NS>
+__global__ void __launch_bounds__(1024, 1) k_dest_hist(const uint32_t *__restrict__ in, size_t n, const SplitArg arg,
                                                       uint32_t *__restrict__ counts)
 {
-    const SplitBinner binner(arg);
+    const SplitBinner<NS> binner(arg);
     __shared__ uint32_t cnt[MAX_SPLITTERS + 1][32];
     for (int i = threadIdx.x; i < (MAX_SPLITTERS + 1) * 32; i += blockDim.x) (&cnt[0][0])[i] = 0;
     __syncthreads();
