@@ -1,6 +1,7 @@
 // engine.cu -- see engine.cuh.
 #include "engine.cuh"
 #include "kernels.cuh"
+#include "onesweep_bulk.cuh"
 
 #include <algorithm>
 #include <atomic>
@@ -52,6 +53,10 @@ using SmemB = OnesweepSmem<SORT_THREADS, BALLOT_KPT, false, RadixBinner::Arg>;
 using SmemSplit = OnesweepSmem<SORT_THREADS, BALLOT_KPT, true, SplitArg>;
 
 #define KERNEL_A(NBITS) k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, RANK_ATOMS, NBITS, SORT_LB, RadixBinner, false>
+#define KERNEL_BULK k_onesweep_bulk<SORT_THREADS, SORT_KPT, SORT_MINB, SORT_LB, RANK_ATOMS, RadixBinner, false>
+using SmemBulk = BulkSmem<SORT_THREADS, SORT_KPT, RadixBinner::Arg>;
+#define KERNEL_SPLIT_BULK(NS) k_onesweep_bulk<SORT_THREADS, BALLOT_KPT, SPLIT_MINB, SORT_LB, RANK_BALLOT, SplitBinner<NS>, true>
+using SmemSplitBulk = BulkSmem<SORT_THREADS, BALLOT_KPT, SplitArg>;
 #define KERNEL_B(NBITS) k_onesweep<SORT_THREADS, BALLOT_KPT, BALLOT_MINB, RANK_BALLOT, NBITS, SORT_LB, RadixBinner, false>
 #define KERNEL_SPLIT(NS) k_onesweep<SORT_THREADS, BALLOT_KPT, SPLIT_MINB, RANK_BALLOT, 0, SORT_LB, SplitBinner<NS>, true>
 
@@ -84,7 +89,7 @@ size_t workspace_bytes(size_t n)
 struct DevInfo {
     bool ready = false;
     int sms = 0;
-    int occ_a = 0, occ_b = 0, occ_split = 0;  // resident CTAs per SM of the three scatter kernels
+    int occ_a = 0, occ_b = 0, occ_split = 0, occ_bulk = 0, occ_split_bulk = 0;  // resident CTAs per SM of the three scatter kernels
     int hist_occ = 0;
     bool rank_atoms = false;  // rank keys with returning shared atomics (self-tested) instead of ballots
 };
@@ -98,6 +103,10 @@ static int env_int(const char *name, int dflt)
 }
 // 1 = bank-private K1 (one 1024-thread CTA per SM), 0 = replicated K1
 static const int g_hist_mode = env_int("LIBSORT_HIST_MODE", 1);
+// 1 = bulk-copy write-out of the scatter pass (k_onesweep_bulk), 0 = LDS + STG write-out (k_onesweep)
+static const int g_bulk_out = env_int("LIBSORT_BULK_OUT", 0);
+// the same choice for the splitter scatter of the distributed sort (runs of kilobytes, peer destinations)
+static const int g_bulk_exchange = env_int("LIBSORT_BULK_EXCHANGE", 1);
 
 template <int NPASS>
 static cudaError_t launch_hist(const uint32_t *in, size_t n, const PassPlan &plan, uint32_t *ghist, int sms, int occ,
@@ -175,6 +184,9 @@ static cudaError_t dev_info(DevInfo **out)
         if (e != cudaSuccess) return e;
         struct { const void *fn; int smem; } kernels[] = {
             {(const void *)KERNEL_A(8), (int)sizeof(SmemA)},     {(const void *)KERNEL_A(0), (int)sizeof(SmemA)},
+            {(const void *)KERNEL_BULK, (int)sizeof(SmemBulk)},
+            {(const void *)KERNEL_SPLIT_BULK(1), (int)sizeof(SmemSplitBulk)}, {(const void *)KERNEL_SPLIT_BULK(3), (int)sizeof(SmemSplitBulk)},
+            {(const void *)KERNEL_SPLIT_BULK(7), (int)sizeof(SmemSplitBulk)}, {(const void *)KERNEL_SPLIT_BULK(15), (int)sizeof(SmemSplitBulk)},
             {(const void *)KERNEL_B(8), (int)sizeof(SmemB)},     {(const void *)KERNEL_B(0), (int)sizeof(SmemB)},
             {(const void *)KERNEL_SPLIT(1), (int)sizeof(SmemSplit)},  {(const void *)KERNEL_SPLIT(3), (int)sizeof(SmemSplit)},
             {(const void *)KERNEL_SPLIT(7), (int)sizeof(SmemSplit)},  {(const void *)KERNEL_SPLIT(15), (int)sizeof(SmemSplit)}};
@@ -183,6 +195,10 @@ static cudaError_t dev_info(DevInfo **out)
             if (e != cudaSuccess) return e;
         }
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.occ_a, KERNEL_A(8), SORT_THREADS, sizeof(SmemA));
+        if (e != cudaSuccess) return e;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.occ_bulk, KERNEL_BULK, SORT_THREADS, sizeof(SmemBulk));
+        if (e != cudaSuccess) return e;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.occ_split_bulk, KERNEL_SPLIT_BULK(15), SORT_THREADS, sizeof(SmemSplitBulk));
         if (e != cudaSuccess) return e;
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.occ_b, KERNEL_B(8), SORT_THREADS, sizeof(SmemB));
         if (e != cudaSuccess) return e;
@@ -350,11 +366,17 @@ cudaError_t sort_bits(const uint32_t *in, uint32_t *a, uint32_t *b, uint32_t *wa
             uint32_t *bcur = base + ((q & 1) * MAX_PASSES + p) * RADIX;
             uint32_t *bnext = (q + 1 < nportions) ? base + (((q + 1) & 1) * MAX_PASSES + p) * RADIX : nullptr;
             const bool full_digit = plan.mask[p] == 0xffu;
-            auto kern = dev->rank_atoms ? (full_digit ? KERNEL_A(8) : KERNEL_A(0)) : (full_digit ? KERNEL_B(8) : KERNEL_B(0));
-            const size_t smem = dev->rank_atoms ? sizeof(SmemA) : sizeof(SmemB);
-            kern<<<grid, SORT_THREADS, smem, st>>>(
-                src + k0, dst, (uint32_t)(k1 - k0), RadixBinner::Arg{plan.shift[p], plan.mask[p]}, bcur, bnext,
-                desc + ((size_t)p * ntiles + t0) * RADIX, tickets + p * MAX_PORTIONS + q, nt, use_tma);
+            const RadixBinner::Arg barg{plan.shift[p], plan.mask[p]};
+            uint32_t *dsc = desc + ((size_t)p * ntiles + t0) * RADIX, *tk = tickets + p * MAX_PORTIONS + q;
+            if (dev->rank_atoms && g_bulk_out && dev->occ_bulk > 0) {
+                const int gridb = (int)std::min<size_t>(nt, (size_t)dev->sms * dev->occ_bulk);
+                KERNEL_BULK<<<gridb, SORT_THREADS, sizeof(SmemBulk), st>>>(src + k0, dst, (uint32_t)(k1 - k0), barg, bcur, bnext, dsc, tk,
+                                                                          nt, use_tma);
+            } else {
+                auto kern = dev->rank_atoms ? (full_digit ? KERNEL_A(8) : KERNEL_A(0)) : (full_digit ? KERNEL_B(8) : KERNEL_B(0));
+                const size_t smem = dev->rank_atoms ? sizeof(SmemA) : sizeof(SmemB);
+                kern<<<grid, SORT_THREADS, smem, st>>>(src + k0, dst, (uint32_t)(k1 - k0), barg, bcur, bnext, dsc, tk, nt, use_tma);
+            }
             launches++;
         }
         tm.mark();
@@ -444,9 +466,18 @@ cudaError_t scatter_by_splitters(const uint32_t *in, size_t n, const uint32_t *s
     k_store_ptrs<<<1, 32, 0, st>>>(t, d_ptrs);
     const int grid = (int)std::min<size_t>(ntiles, (size_t)dev->sms * dev->occ_split);
     const int use_tma = (reinterpret_cast<uintptr_t>(in) & 15u) == 0;
-    auto kern = nsplit <= 1 ? KERNEL_SPLIT(1) : nsplit <= 3 ? KERNEL_SPLIT(3) : nsplit <= 7 ? KERNEL_SPLIT(7) : KERNEL_SPLIT(15);
-    kern<<<grid, SORT_THREADS, sizeof(SmemSplit), st>>>(in, nullptr, (uint32_t)n, SplitArg{splitters, nsplit}, d_ptrs, nullptr,
-                                                        ws + WS_DESC, ws + WS_TICKET, (uint32_t)ntiles, use_tma);
+    const SplitArg arg{splitters, nsplit};
+    if (g_bulk_exchange && dev->occ_split_bulk > 0) {
+        auto kern = nsplit <= 1 ? KERNEL_SPLIT_BULK(1) : nsplit <= 3 ? KERNEL_SPLIT_BULK(3) : nsplit <= 7 ? KERNEL_SPLIT_BULK(7)
+                                                                                                        : KERNEL_SPLIT_BULK(15);
+        const int gridb = (int)std::min<size_t>(ntiles, (size_t)dev->sms * dev->occ_split_bulk);
+        kern<<<gridb, SORT_THREADS, sizeof(SmemSplitBulk), st>>>(in, nullptr, (uint32_t)n, arg, d_ptrs, nullptr, ws + WS_DESC,
+                                                                 ws + WS_TICKET, (uint32_t)ntiles, use_tma);
+    } else {
+        auto kern = nsplit <= 1 ? KERNEL_SPLIT(1) : nsplit <= 3 ? KERNEL_SPLIT(3) : nsplit <= 7 ? KERNEL_SPLIT(7) : KERNEL_SPLIT(15);
+        kern<<<grid, SORT_THREADS, sizeof(SmemSplit), st>>>(in, nullptr, (uint32_t)n, arg, d_ptrs, nullptr, ws + WS_DESC,
+                                                            ws + WS_TICKET, (uint32_t)ntiles, use_tma);
+    }
     return cudaGetLastError();
 }
 

@@ -1,0 +1,249 @@
+// onesweep_bulk.cuh -- the scatter pass with a bulk-copy write-out.
+//
+// Same contract and the same phases (1)-(5) as k_onesweep<RANK_ATOMS, RadixBinner>
+// in kernels.cuh, but the digit-sorted tile is laid out in shared memory so that
+// every bucket's run has the same 16-byte phase as its destination in global
+// memory.  One thread per bucket then hands the 16 B-aligned body of its run to
+// the bulk-copy engine (cp.async.bulk.global.shared::cta, SASS UBLKCP.G.S) and
+// stores the <= 3 keys of the ragged head and tail itself.  The write-out costs
+// no LDS/STG wavefronts for the body, which matters because the pass is bound by
+// the L1/shared-memory pipe (profiles/r01b_k_onesweep_lsu_wavefronts.txt), not
+// by HBM.  The price: the look-back must finish before the tile is re-ordered,
+// because the layout depends on the global offsets modulo 4 keys.
+#pragma once
+#include "kernels.cuh"
+
+namespace b200sort {
+
+__device__ __forceinline__ void bulk_store(void *dst_gmem, const void *src_smem, uint32_t bytes)
+{
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_gmem), "r"(smem_u32(src_smem)),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// wait until the bulk copies of this thread have finished READING shared memory
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+
+template <int THREADS, int KPT, class BinnerArg>
+struct BulkSmem {
+    static constexpr int KEYS_PER_THREAD = KPT;
+    static constexpr int TILE = THREADS * KPT;
+    static constexpr int NWARPS = THREADS / 32;
+    static constexpr int PAD = RADIX * 6;      // <= 3 keys of head and of tail padding per bucket
+    alignas(128) uint32_t keys[TILE + PAD];    // TMA landing buffer [0, TILE), then the padded digit-sorted tile
+    uint32_t warp_hist[NWARPS][RADIX];         // per-warp digit counters -> running BYTE offsets into keys[]
+    uint32_t s_warp[8];
+    alignas(8) uint64_t mbar;
+    uint32_t next_tile;
+    BinnerArg binner_arg;                      // copy for the out-of-line heavy-tile path
+    uint32_t heavy_d4;
+};
+
+// RANK / Binner / PTR_OUT as in k_onesweep: with PTR_OUT `base_v` holds one 64-bit
+// destination address per bin (local or NVLink-mapped peer memory) -- the splitter
+// scatter of the distributed sort, where a tile has at most 16 long runs and the
+// bulk-copy engine, not the SM's store path, rides out the NVLink latency.
+template <int THREADS, int KPT, int MINB, int LB, int RANK, class Binner, bool PTR_OUT>
+__global__ void __launch_bounds__(THREADS, MINB)
+    k_onesweep_bulk(const uint32_t *__restrict__ in, uint32_t *__restrict__ out, uint32_t n, const typename Binner::Arg binner_arg,
+                    const void *__restrict__ base_v, uint32_t *__restrict__ base_next, uint32_t *__restrict__ desc,
+                    uint32_t *__restrict__ ticket, uint32_t ntiles, int use_tma)
+{
+    using Smem = BulkSmem<THREADS, KPT, typename Binner::Arg>;
+    constexpr int TILE = Smem::TILE;
+    constexpr int NWARPS = Smem::NWARPS;
+    static_assert(THREADS >= RADIX, "need one thread per bin");
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    Smem &s = *reinterpret_cast<Smem *>(smem_raw);
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const Binner binner(binner_arg);
+    const uint32_t pad_bin = binner.pad_bin();
+    unsigned char *const my_hist = reinterpret_cast<unsigned char *>(s.warp_hist[warp]);
+    unsigned char *const tile_bytes = reinterpret_cast<unsigned char *>(s.keys);
+
+    auto issue_load = [&](uint32_t tile) {
+        const uint32_t valid = min((uint32_t)TILE, n - tile * (uint32_t)TILE);
+        const uint32_t bytes = (valid * 4u) & ~15u;
+        if (bytes) {
+            mbar_arrive_expect_tx(&s.mbar, bytes);
+            tma_load_1d(s.keys, in + (size_t)tile * TILE, bytes, &s.mbar);
+        } else {
+            mbar_arrive_expect_tx(&s.mbar, 0);
+        }
+    };
+
+    if (tid == 0) {
+        mbar_init(&s.mbar, 1);
+        fence_mbar_init();
+        const uint32_t t = atomicAdd(ticket, 1u);
+        s.next_tile = t;
+        s.binner_arg = binner_arg;
+        if (use_tma && t < ntiles) issue_load(t);
+    }
+#pragma unroll
+    for (int j = lane; j < RADIX; j += 32) s.warp_hist[warp][j] = 0;
+    __syncthreads();
+    uint32_t cur = s.next_tile;
+
+    for (uint32_t it = 0; cur < ntiles; ++it) {
+        const uint32_t tile_base = cur * (uint32_t)TILE;
+        const uint32_t valid = min((uint32_t)TILE, n - tile_base);
+
+        // (1) keys -> registers, warp-striped so that tile order == rank order
+        uint32_t key[KPT];
+        const uint32_t wbase = warp * (KPT * 32) + lane;
+        if (use_tma) {
+            mbar_wait(&s.mbar, it & 1);
+            if (valid == TILE) {
+#pragma unroll
+                for (int i = 0; i < KPT; i++) key[i] = s.keys[wbase + i * 32];
+            } else {
+                const uint32_t staged = ((valid * 4u) & ~15u) >> 2;
+#pragma unroll
+                for (int i = 0; i < KPT; i++) {
+                    const uint32_t idx = wbase + i * 32;
+                    key[i] = idx < staged ? s.keys[idx] : (idx < valid ? in[(size_t)tile_base + idx] : 0xffffffffu);
+                }
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < KPT; i++) {
+                const uint32_t idx = wbase + i * 32;
+                key[i] = idx < valid ? in[(size_t)tile_base + idx] : 0xffffffffu;
+            }
+        }
+        __syncwarp();  // this warp's counters were zeroed by other lanes
+
+        // (2) early counts: per-warp digit histogram (see k_onesweep for the bin()/bin4() note)
+#pragma unroll
+        for (int i = 0; i < KPT; i++) atomicAdd(&s.warp_hist[warp][binner.bin(key[i])], 1u);
+        __syncthreads();
+
+        // (3) bin threads: reduce over warps, publish the tile aggregate, finish the
+        //     look-back, then lay the buckets out with the 16-byte phase of their destinations
+        uint32_t my_count = 0, padded = 0, phase = 0, span4 = 0;
+        unsigned long long dst_addr = 0;  // byte address of the first destination of this tile's run
+        if (tid < RADIX) {
+#pragma unroll
+            for (int w = 0; w < NWARPS; w++) padded += s.warp_hist[w][tid];
+            my_count = padded;
+            if ((uint32_t)tid == pad_bin) my_count -= (uint32_t)TILE - valid;  // padding keys carry the top digit
+            st_relaxed(&desc[(size_t)cur * RADIX + tid], (cur == 0 ? DESC_INCL : DESC_AGG) | my_count);
+
+            uint32_t excl = 0;
+            if (cur != 0) {
+                // windowed decoupled look-back: LB descriptors per round trip
+                uint32_t j = cur - 1;
+                bool done = false;
+                while (true) {
+                    uint32_t lbv[LB];
+#pragma unroll
+                    for (int k = 0; k < LB; k++)
+                        lbv[k] = (uint32_t)k <= j ? ld_relaxed(&desc[(size_t)(j - k) * RADIX + tid]) : DESC_INCL;
+#pragma unroll
+                    for (int k = 0; k < LB; k++) {
+                        if (!done) {
+                            const uint32_t v = lbv[k];
+                            if ((v >> 30) == 0) break;
+                            excl += v & DESC_VAL;
+                            if (v & DESC_INCL) done = true;
+                            else --j;
+                        }
+                    }
+                    if (done) break;
+                }
+                st_relaxed(&desc[(size_t)cur * RADIX + tid], DESC_INCL | (excl + my_count));
+            }
+            if (PTR_OUT) {
+                dst_addr = static_cast<const unsigned long long *>(base_v)[tid] + 4ull * excl;
+            } else {
+                const uint32_t gbase = static_cast<const uint32_t *>(base_v)[tid];
+                dst_addr = reinterpret_cast<unsigned long long>(out) + 4ull * ((unsigned long long)gbase + excl);
+                if (base_next && cur == ntiles - 1) base_next[tid] = gbase + excl + my_count;
+            }
+            phase = (uint32_t)(dst_addr >> 2) & 3u;       // keys before it in its 16-byte chunk
+            span4 = padded ? ((phase + padded + 3u) & ~3u) * 4u : 0u;  // bytes taken in the padded layout
+        }
+        const uint32_t slot4 = block_excl_scan_256(span4, s.s_warp, nullptr);
+        const uint32_t start4 = slot4 + phase * 4u;       // byte offset of the run in keys[]
+        const bool is_heavy = RANK == RANK_ATOMS && padded * 4u > (uint32_t)TILE;  // one digit holds > 1/4 of the tile
+        if (tid < RADIX) {
+            uint32_t run = start4;
+#pragma unroll
+            for (int w = 0; w < NWARPS; w++) {
+                const uint32_t c = s.warp_hist[w][tid];
+                s.warp_hist[w][tid] = run;
+                run += c << 2;
+            }
+            if (is_heavy) s.heavy_d4 = (uint32_t)tid * 4u;
+        }
+        const int heavy = __syncthreads_or(is_heavy);
+
+        // (4) rank every key and move it to its place in the padded digit-sorted tile
+        if (RANK == RANK_ATOMS) {
+            if (!heavy) {
+#pragma unroll
+                for (int i = 0; i < KPT; i++) {
+                    const uint32_t p4 = atomicAdd(reinterpret_cast<uint32_t *>(my_hist + binner.bin4(key[i])), 4u);
+                    *reinterpret_cast<uint32_t *>(tile_bytes + p4) = key[i];
+                }
+            } else {
+                uint32_t spilled[KPT];
+#pragma unroll
+                for (int i = 0; i < KPT; i++) spilled[i] = key[i];
+                rank_tile_heavy<Binner, Smem>(spilled, &s);
+            }
+        } else {
+            const uint32_t lt = lanemask_lt();
+            const int nbits = binner.nbits();
+            const uint32_t hist_addr = smem_u32(my_hist);
+#pragma unroll
+            for (int i = 0; i < KPT; i++) {
+                const uint32_t d4 = binner.bin4(key[i]);
+                const uint32_t peers = match_digit<0>(d4 >> 2, nbits);
+                const uint32_t before = __popc(peers & lt);
+                const int top = 31 - __clz(peers);  // highest peer lane leads; its `before` + 1 is the group size
+                uint32_t off4 = leader_atom_add(hist_addr + d4, (before + 1u) * 4u, lane == top);
+                off4 = __shfl_sync(0xffffffffu, off4, top);
+                *reinterpret_cast<uint32_t *>(tile_bytes + off4 + before * 4u) = key[i];
+            }
+        }
+        __syncwarp();
+#pragma unroll
+        for (int j = lane; j < RADIX; j += 32) s.warp_hist[warp][j] = 0;
+        uint32_t t_next = 0;
+        if (tid == 0) t_next = atomicAdd(ticket, 1u);  // in flight during the write-out
+        __syncthreads();
+
+        // (5) write-out: thread d owns bucket d.  Head and tail (the keys outside whole
+        //     16-byte chunks of the destination) are stored one by one, the body goes to
+        //     the bulk-copy engine.
+        if (tid < RADIX && my_count) {
+            const uint32_t *src = reinterpret_cast<const uint32_t *>(tile_bytes + start4);
+            uint32_t *dst = reinterpret_cast<uint32_t *>(dst_addr);
+            const uint32_t head = min(my_count, (4u - phase) & 3u);
+            const uint32_t body = (my_count - head) & ~3u;
+            for (uint32_t j = 0; j < head; j++) dst[j] = src[j];
+            for (uint32_t j = head + body; j < my_count; j++) dst[j] = src[j];
+            if (body) {
+                fence_proxy_async();  // the generic-proxy stores of (4) come before the engine's reads
+                bulk_store(dst + head, src + head, body * 4u);
+                bulk_commit();
+                bulk_wait_read();
+            }
+        }
+        if (tid == 0) s.next_tile = t_next;
+        __syncthreads();  // the tile buffer is free again
+        cur = s.next_tile;
+        if (tid == 0 && use_tma && cur < ntiles) {
+            fence_proxy_async();
+            issue_load(cur);
+        }
+    }
+    // bulk stores still in flight belong to this thread's bulk async-group: drain them
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
+}  // namespace b200sort
