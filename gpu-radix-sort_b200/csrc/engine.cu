@@ -341,7 +341,9 @@ cudaError_t sort_bits(const uint32_t *in, uint32_t *a, uint32_t *b, uint32_t *wa
     launches++;
     tm.mark();
     const bool bounds_from_hist = d_bounds && P == 1 && plan.mask[0] == ngroups - 1;
-    k_scan_hist<<<P, RADIX, 0, st>>>(ghist, base, bounds_from_hist ? d_bounds : nullptr, (uint32_t)ngroups);
+    // constant-digit passes become copies (single-portion inputs only: the copy's destination is `dst` itself)
+    k_scan_hist<<<P, RADIX, 0, st>>>(ghist, base, bounds_from_hist ? d_bounds : nullptr, (uint32_t)ngroups, (uint32_t)n,
+                                     nportions == 1 ? tickets + SKIP_OFFSET : nullptr);
     launches++;
     tm.mark();
 

@@ -173,8 +173,14 @@ __device__ __forceinline__ uint32_t block_excl_scan_256(uint32_t v, uint32_t *s_
 // One 256-thread CTA per pass: base[p][b] = #keys whose digit p is < b.
 // When d_exact != nullptr (single-pass partial sort, width <= 8) the scan of
 // pass 0 IS the exact boundary array (localTest/tests.cpp:44-54).
+// skip (nullable): skip[p * SKIP_STRIDE] = 1 when every key has the same digit in pass p
+// (one bin holds all n keys) -- that pass is the identity permutation and the scatter
+// kernel just copies.
+constexpr int SKIP_STRIDE = 8;   // one flag per (pass, portion) slot, beside the tile tickets
+constexpr int SKIP_OFFSET = 32;  // flag of a pass = its ticket word + SKIP_OFFSET
 __global__ void __launch_bounds__(256) k_scan_hist(const uint32_t *__restrict__ ghist, uint32_t *__restrict__ base,
-                                                  uint32_t *__restrict__ d_exact, uint32_t ngroups)
+                                                  uint32_t *__restrict__ d_exact, uint32_t ngroups, uint32_t n,
+                                                  uint32_t *__restrict__ skip)
 {
     __shared__ uint32_t s_warp[8];
     const int p = blockIdx.x;
@@ -182,6 +188,19 @@ __global__ void __launch_bounds__(256) k_scan_hist(const uint32_t *__restrict__ 
     uint32_t ex = block_excl_scan_256(c, s_warp, nullptr);
     base[p * RADIX + threadIdx.x] = ex;
     if (d_exact && p == 0 && threadIdx.x < ngroups) d_exact[threadIdx.x] = ex;
+    if (skip && c == n) skip[p * SKIP_STRIDE] = 1;
+}
+
+// The copy a scatter pass degenerates to when its digit is constant over the whole input.
+__device__ __forceinline__ void copy_keys(const uint32_t *__restrict__ in, uint32_t *__restrict__ out, uint32_t n)
+{
+    const uint32_t stride = gridDim.x * blockDim.x;
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    for (; i + 3 * stride < n; i += 4 * stride) {
+        const uint32_t a = in[i], b = in[i + stride], c = in[i + 2 * stride], d = in[i + 3 * stride];
+        out[i] = a; out[i + stride] = b; out[i + 2 * stride] = c; out[i + 3 * stride] = d;
+    }
+    for (; i < n; i += stride) out[i] = in[i];
 }
 
 // ---------------------------------------------------------------- K3 ------
@@ -344,6 +363,10 @@ __global__ void __launch_bounds__(THREADS, MINB)
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Smem &s = *reinterpret_cast<Smem *>(smem_raw);
 
+    if (!PTR_OUT && ticket[SKIP_OFFSET]) {  // constant digit (k_scan_hist): the pass is a copy
+        copy_keys(in, out, n);
+        return;
+    }
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const Binner binner(binner_arg);
     const uint32_t pad_bin = binner.pad_bin();

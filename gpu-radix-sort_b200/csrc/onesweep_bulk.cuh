@@ -57,6 +57,10 @@ __global__ void __launch_bounds__(THREADS, MINB)
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Smem &s = *reinterpret_cast<Smem *>(smem_raw);
 
+    if (!PTR_OUT && ticket[SKIP_OFFSET]) {  // constant digit (k_scan_hist): the pass is a copy
+        copy_keys(in, out, n);
+        return;
+    }
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const Binner binner(binner_arg);
     const uint32_t pad_bin = binner.pad_bin();

@@ -227,3 +227,17 @@ def test_cxx_consumers(gpu_lib, pkg):
     if os.path.exists(ref_exe):
         r = subprocess.run([ref_exe], capture_output=True, text=True, timeout=300)   # runBenches(): 16-bit partial, 2^28 keys
         assert r.returncode == 0 and "Partial sort (16b)" in r.stdout, r.stdout + r.stderr
+
+
+@pytest.mark.parametrize("env", [{}, {"LIBSORT_RANK": "ballot"}, {"LIBSORT_BULK_OUT": "1"}, {"LIBSORT_RANK": "atoms"}],
+                         ids=["default", "ballot", "bulk_out", "atoms_forced"])
+def test_kernel_variants(env):
+    """Every compiled scatter kernel (ranking mode x write-out) against the oracle, multi-tile
+    skewed inputs included; the variant is fixed when the library is first used, hence a fresh process."""
+    import subprocess
+    import sys
+    e = dict(os.environ)
+    e.update(env)
+    r = subprocess.run([sys.executable, os.path.join(os.path.dirname(__file__), "variant_worker.py")], env=e,
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
