@@ -25,7 +25,8 @@ class KernelTimes(ctypes.Structure):
 
 
 def lib_path():
-    return os.path.join(_LIBDIR, "libsort.so")
+    # LIBSORT_SO: developer override used by the kernel-shape sweeps (tools/gpu_*.sh)
+    return os.environ.get("LIBSORT_SO") or os.path.join(_LIBDIR, "libsort.so")
 
 
 def build(verbose=False):

@@ -241,3 +241,16 @@ def test_kernel_variants(env):
     r = subprocess.run([sys.executable, os.path.join(os.path.dirname(__file__), "variant_worker.py")], env=e,
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+@pytest.mark.parametrize("bulk", ["1", "0"], ids=["bulk_copy", "lds_stg"])
+def test_splitter_scatter_single_gpu(bulk):
+    """Counts per destination and the stable splitter scatter (both write-out kernels, 2..16
+    destinations, every compiled splitter capacity) on one GPU against numpy."""
+    import subprocess
+    import sys
+    e = dict(os.environ)
+    e["LIBSORT_BULK_EXCHANGE"] = bulk
+    r = subprocess.run([sys.executable, os.path.join(os.path.dirname(__file__), "split_worker.py")], env=e,
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
