@@ -60,7 +60,7 @@ using SmemSplitBulk = BulkSmem<SORT_THREADS, BALLOT_KPT, SplitArg>;
 #define KERNEL_B(NBITS) k_onesweep<SORT_THREADS, BALLOT_KPT, BALLOT_MINB, RANK_BALLOT, NBITS, SORT_LB, RadixBinner, false>
 #define KERNEL_SPLIT(NS) k_onesweep<SORT_THREADS, BALLOT_KPT, SPLIT_MINB, RANK_BALLOT, 0, SORT_LB, SplitBinner<NS>, true>
 
-int tile_keys() { return kTileA; }
+
 
 // workspace layout, in uint32 words
 constexpr size_t WS_HIST = 0;                                   // [4][256]
@@ -219,6 +219,12 @@ static cudaError_t dev_info(DevInfo **out)
     }
     *out = &d;
     return cudaSuccess;
+}
+
+int tile_keys()
+{
+    DevInfo *dev = nullptr;  // the tile of the kernels this device runs (atomic or ballot ranking)
+    return (dev_info(&dev) == cudaSuccess && !dev->rank_atoms) ? kTileB : kTileA;
 }
 
 static PassPlan make_plan(uint32_t offset, uint32_t width)

@@ -213,9 +213,18 @@ __device__ __forceinline__ void copy_keys(const uint32_t *__restrict__ in, uint3
 // instructions (LOP3 -> predicate, VOTE, SEL, LOP3): peers &= ballot(bit) ^ (bit ? 0 : ~0).
 __device__ __forceinline__ uint32_t match_bit(uint32_t peers, uint32_t d, uint32_t bitmask)
 {
-    const bool bit = (d & bitmask) != 0;
-    const uint32_t m = __ballot_sync(0xffffffffu, bit);
-    return peers & (m ^ (bit ? 0u : 0xffffffffu));
+    asm("{\n\t"
+        ".reg .pred p;\n\t"
+        ".reg .b32 t, m, x;\n\t"
+        "and.b32 t, %1, %2;\n\t"
+        "setp.ne.u32 p, t, 0;\n\t"
+        "vote.sync.ballot.b32 m, p, 0xffffffff;\n\t"
+        "selp.b32 x, 0, -1, p;\n\t"
+        "lop3.b32 %0, %0, m, x, 0x60;\n\t"
+        "}"
+        : "+r"(peers)
+        : "r"(d), "r"(bitmask));
+    return peers;
 }
 
 template <int NBITS>
@@ -545,30 +554,32 @@ __global__ void __launch_bounds__(THREADS, MINB)
         if (tid == 0) t_next = atomicAdd(ticket, 1u);  // in flight during the write-out
         __syncthreads();
 
-        // (6) coalesced write-out: consecutive threads, consecutive sorted keys
-        auto put = [&](uint32_t p) {
-            const uint32_t k = s.keys[p];
-            const uint32_t d4 = binner.bin4(k);
-            if (PTR_OUT)
-                *reinterpret_cast<uint32_t *>(*reinterpret_cast<const unsigned long long *>(
-                                                  reinterpret_cast<const unsigned char *>(s.tile_dst) + 2 * d4) +
-                                              4ull * p) = k;
-            else
-                out[*reinterpret_cast<const uint32_t *>(reinterpret_cast<const unsigned char *>(s.tile_dst) + d4) + p] = k;
-        };
-        if (valid == TILE) {
+        // (6) coalesced write-out: consecutive threads, consecutive sorted keys.  The sorted
+        //     keys go to registers first; from the barrier on the tile buffer is free, so the
+        //     next tile's bulk load runs under this tile's stores.
 #pragma unroll
-            for (int i = 0; i < KPT; i++) put(tid + i * THREADS);
-        } else {
-            for (uint32_t p = tid; p < valid; p += THREADS) put(p);
-        }
+        for (int i = 0; i < KPT; i++) key[i] = s.keys[tid + i * THREADS];
         if (tid == 0) s.next_tile = t_next;
-        __syncthreads();  // the tile buffer is free again
-        cur = s.next_tile;
-        if (tid == 0 && use_tma && cur < ntiles) {
+        __syncthreads();
+        const uint32_t nxt = s.next_tile;
+        if (tid == 0 && use_tma && nxt < ntiles) {
             fence_proxy_async();  // generic-proxy accesses to keys[] come before the bulk copy's writes
-            issue_load(cur);
+            issue_load(nxt);
         }
+#pragma unroll
+        for (int i = 0; i < KPT; i++) {
+            const uint32_t p = tid + i * THREADS;
+            const uint32_t d4 = binner.bin4(key[i]);
+            if (valid == TILE || p < valid) {
+                if (PTR_OUT)
+                    *reinterpret_cast<uint32_t *>(*reinterpret_cast<const unsigned long long *>(
+                                                      reinterpret_cast<const unsigned char *>(s.tile_dst) + 2 * d4) +
+                                                  4ull * p) = key[i];
+                else
+                    out[*reinterpret_cast<const uint32_t *>(reinterpret_cast<const unsigned char *>(s.tile_dst) + d4) + p] = key[i];
+            }
+        }
+        cur = nxt;
     }
 }
 
