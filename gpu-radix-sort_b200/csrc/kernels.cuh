@@ -285,12 +285,34 @@ struct SplitBinner {
 #pragma unroll
         for (int j = 0; j < NS; j++) v[j] = j < a.nsplit ? a.d_splitters[j] : 0xffffffffu;
     }
+    // number of splitters <= key.  Unused slots hold 0xffffffff; the min() undoes what a key of
+    // 0xffffffff would count against them.  NS >= 7: branch-free binary search (3 or 4 compares
+    // and a few selects instead of NS compares).
     __device__ __forceinline__ uint32_t bin(uint32_t key) const
     {
         uint32_t d = 0;
+        if (NS == 7) {
+            const bool c2 = key >= v[3];
+            const uint32_t m1 = c2 ? v[5] : v[1];
+            const bool c1 = key >= m1;
+            const uint32_t lo = c1 ? v[2] : v[0], hi = c1 ? v[6] : v[4];
+            const bool c0 = key >= (c2 ? hi : lo);
+            d = (c2 ? 4u : 0u) + (c1 ? 2u : 0u) + (c0 ? 1u : 0u);
+        } else if (NS == 15) {
+            const bool c3 = key >= v[7];
+            const uint32_t m2 = c3 ? v[11] : v[3];
+            const bool c2 = key >= m2;
+            const uint32_t a = c2 ? v[5] : v[1], b = c2 ? v[13] : v[9];
+            const bool c1 = key >= (c3 ? b : a);
+            const uint32_t q0 = c1 ? v[2] : v[0], q1 = c1 ? v[6] : v[4], q2 = c1 ? v[10] : v[8], q3 = c1 ? v[14] : v[12];
+            const uint32_t r0 = c2 ? q1 : q0, r1 = c2 ? q3 : q2;
+            const bool c0 = key >= (c3 ? r1 : r0);
+            d = (c3 ? 8u : 0u) + (c2 ? 4u : 0u) + (c1 ? 2u : 0u) + (c0 ? 1u : 0u);
+        } else {
 #pragma unroll
-        for (int j = 0; j < NS; j++) d += (j < nsplit && key >= v[j]) ? 1u : 0u;
-        return d;
+            for (int j = 0; j < NS; j++) d += key >= v[j] ? 1u : 0u;
+        }
+        return min(d, (uint32_t)nsplit);
     }
     __device__ __forceinline__ uint32_t bin4(uint32_t key) const { return bin(key) << 2; }
     __device__ __forceinline__ uint32_t pad_bin() const { return (uint32_t)nsplit; }
