@@ -12,7 +12,7 @@ LEGACY_SYMBOLS = ["initLibSort", "gpuPartial", "providedGpu", "providedCpu", "po
 ADDITIVE_SYMBOLS = ["libsortTileKeys", "libsortWorkspaceBytes", "libsortDeviceSort", "libsortDeviceCount",
                     "libsortReleaseCaches", "libsortErrorString", "libsortDebugSetPortionTiles",
                     "libsortDeviceSample", "libsortDevicePickSplitters", "libsortDeviceSplitCounts", "libsortPopulateInputAt", "libsortDeviceScatterToPeers",
-                    "libsortIpcAlloc", "libsortIpcFree", "libsortIpcExport", "libsortIpcOpen", "libsortIpcClose"]
+                    "libsortIpcAlloc", "libsortIpcFree", "libsortIpcExport", "libsortIpcOpen", "libsortIpcClose", "libsortDistribSort"]
 
 BOUNDS_REFERENCE = 0
 BOUNDS_EXACT = 1
@@ -96,6 +96,8 @@ def lib():
     for name in ("libsortDeviceSample", "libsortDevicePickSplitters", "libsortDeviceSplitCounts", "libsortPopulateInputAt", "libsortDeviceScatterToPeers", "libsortIpcAlloc",
                  "libsortIpcFree", "libsortIpcExport", "libsortIpcOpen", "libsortIpcClose"):
         getattr(L, name).restype = ci
+    L.libsortDistribSort.argtypes = [vp, sz, ci]
+    L.libsortDistribSort.restype = ci
     _lib = L
     return L
 

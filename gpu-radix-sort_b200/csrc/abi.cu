@@ -44,6 +44,14 @@ struct DeviceCtx {
     uint32_t *d_bounds = nullptr;
     size_t bounds_cap = 0;
     HostCopier copier;
+    // single-process distributed sort (libsortDistribSort)
+    uint32_t *recv = nullptr;   // keys arriving from every GPU
+    size_t recv_cap = 0;
+    uint32_t *small = nullptr;  // samples | splitters | counts
+    uint32_t *gather = nullptr; // device 0: all samples | sorted | scratch
+    size_t gather_cap = 0;
+    void *ws_small = nullptr;
+    size_t ws_small_cap = 0;
 };
 
 struct Pool {
@@ -100,7 +108,53 @@ struct Reservation {
             c->busy = false;
             g_pool.free_count++;
         }
-        g_pool.cv.notify_one();
+        g_pool.cv.notify_all();
+    }
+};
+
+// All of the first `want` GPUs at once (want <= 0: the whole pool), taken in
+// index order so that concurrent callers cannot hold each other's devices.
+struct MultiReservation {
+    std::vector<DeviceCtx *> cs;
+    bool acquire(int want)
+    {
+        std::unique_lock<std::mutex> lk(g_pool.mu);
+        if (!g_pool.inited) {
+            fprintf(stderr, "libsort: initLibSort() has not been called\n");
+            return false;
+        }
+        const int have = (int)g_pool.ctx.size();
+        if (want <= 0) want = have;
+        if (want > have) {
+            fprintf(stderr, "libsort: %d GPUs requested, the pool has %d\n", want, have);
+            return false;
+        }
+        for (int i = 0; i < want; i++) {
+            DeviceCtx *x = &g_pool.ctx[i];
+            g_pool.cv.wait(lk, [x] { return !x->busy; });
+            x->busy = true;
+            g_pool.free_count--;
+            cs.push_back(x);
+        }
+        lk.unlock();
+        for (DeviceCtx *c : cs) {
+            if (!cuda_ok(cudaSetDevice(c->dev), "cudaSetDevice")) return false;
+            if (!c->stream && !cuda_ok(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking), "cudaStreamCreate"))
+                return false;
+        }
+        return true;
+    }
+    ~MultiReservation()
+    {
+        if (cs.empty()) return;
+        {
+            std::lock_guard<std::mutex> lk(g_pool.mu);
+            for (DeviceCtx *c : cs) {
+                c->busy = false;
+                g_pool.free_count++;
+            }
+        }
+        g_pool.cv.notify_all();
     }
 };
 
@@ -112,10 +166,14 @@ void free_ctx_buffers(DeviceCtx &c)
     if (c.b) cudaFree(c.b);
     if (c.ws) cudaFree(c.ws);
     if (c.d_bounds) cudaFree(c.d_bounds);
-    c.a = c.b = nullptr;
-    c.ws = nullptr;
+    if (c.recv) cudaFree(c.recv);
+    if (c.small) cudaFree(c.small);
+    if (c.gather) cudaFree(c.gather);
+    if (c.ws_small) cudaFree(c.ws_small);
+    c.a = c.b = c.recv = c.small = c.gather = nullptr;
+    c.ws = c.ws_small = nullptr;
     c.d_bounds = nullptr;
-    c.cap_keys = c.ws_cap = c.bounds_cap = 0;
+    c.cap_keys = c.ws_cap = c.bounds_cap = c.recv_cap = c.gather_cap = c.ws_small_cap = 0;
     c.copier.release();
 }
 
@@ -392,3 +450,214 @@ API int libsortIpcOpen(const void *handle64, void **ptr)
     return (int)cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess);
 }
 API int libsortIpcClose(void *ptr) { return (int)cudaIpcCloseMemHandle(ptr); }
+
+// ---- single-process multi-GPU sort ---------------------------------------------
+// The whole distributed sort behind one host-pointer call, for callers that own
+// every GPU of the box from one process (the cgo benchmark driver, reference
+// benchmark/pkg/sort/distrib.go:183-248; the C++ twin localTest/benchmarks.cpp:
+// 70-160).  Same algorithm as the one-rank-per-GPU Python driver (distrib.py):
+// sample -> splitters -> destination counts -> ONE fused partition + exchange
+// kernel per GPU storing straight into its peers' receive buffers over NVLink
+// -> local 4-pass sort.  The tiny all-gathers (samples, count matrix) are peer
+// copies / host reads because one thread drives every device.
+namespace {
+
+constexpr uint32_t kDistSamples = 1u << 15;  // per GPU
+constexpr int kDistMaxGpus = 16;             // SplitBinner holds 15 splitters
+
+bool dist_small_buffers(DeviceCtx &c, int P, bool root)
+{
+    if (!c.small && !cuda_ok(cudaMalloc(&c.small, (kDistSamples + 32) * sizeof(uint32_t)), "cudaMalloc(samples)"))
+        return false;
+    if (!root) return true;
+    const size_t all = (size_t)P * kDistSamples;
+    if (all > c.gather_cap) {
+        if (c.gather) cudaFree(c.gather);
+        c.gather = nullptr;
+        c.gather_cap = 0;
+        if (!cuda_ok(cudaMalloc(&c.gather, 3 * all * sizeof(uint32_t)), "cudaMalloc(sample gather)")) return false;
+        c.gather_cap = all;
+    }
+    const size_t need = workspace_bytes(all);
+    if (need > c.ws_small_cap) {
+        if (c.ws_small) cudaFree(c.ws_small);
+        c.ws_small = nullptr;
+        c.ws_small_cap = 0;
+        if (!cuda_ok(cudaMalloc(&c.ws_small, need), "cudaMalloc(sample workspace)")) return false;
+        c.ws_small_cap = need;
+    }
+    return true;
+}
+
+bool dist_recv_buffer(DeviceCtx &c, size_t keys)
+{
+    if (keys <= c.recv_cap) return true;
+    if (c.recv) cudaFree(c.recv);
+    c.recv = nullptr;
+    c.recv_cap = 0;
+    const size_t cap = (keys + keys / 16 + 1023) & ~(size_t)1023;
+    if (!cuda_ok(cudaMalloc(&c.recv, cap * sizeof(uint32_t)), "cudaMalloc(receive buffer)")) return false;
+    c.recv_cap = cap;
+    return true;
+}
+
+bool dist_enable_peers(const std::vector<DeviceCtx *> &cs)
+{
+    static std::mutex mu;
+    static bool done[kDistMaxGpus][kDistMaxGpus] = {};
+    std::lock_guard<std::mutex> lk(mu);
+    for (DeviceCtx *a : cs)
+        for (DeviceCtx *b : cs) {
+            if (a == b || done[a->dev][b->dev]) continue;
+            int can = 0;
+            if (!cuda_ok(cudaDeviceCanAccessPeer(&can, a->dev, b->dev), "cudaDeviceCanAccessPeer")) return false;
+            if (!can) {
+                fprintf(stderr, "libsort: GPU %d cannot address GPU %d's memory (no NVLink/P2P)\n", a->dev, b->dev);
+                return false;
+            }
+            if (!cuda_ok(cudaSetDevice(a->dev), "cudaSetDevice")) return false;
+            cudaError_t e = cudaDeviceEnablePeerAccess(b->dev, 0);
+            if (e == cudaErrorPeerAccessAlreadyEnabled) {
+                cudaGetLastError();
+                e = cudaSuccess;
+            }
+            if (!cuda_ok(e, "cudaDeviceEnablePeerAccess")) return false;
+            done[a->dev][b->dev] = true;
+        }
+    return true;
+}
+
+bool dist_sync_all(const std::vector<DeviceCtx *> &cs, int P, const char *what)
+{
+    for (int g = 0; g < P; g++) {
+        if (!cuda_ok(cudaSetDevice(cs[g]->dev), "cudaSetDevice")) return false;
+        if (!cuda_ok(cudaStreamSynchronize(cs[g]->stream), what)) return false;
+    }
+    return true;
+}
+
+}  // namespace
+
+API int libsortDistribSort(uint32_t *h_keys, size_t n, int ngpu)
+{
+    if (ngpu > kDistMaxGpus) {
+        fprintf(stderr, "libsort: at most %d GPUs per distributed sort\n", kDistMaxGpus);
+        return 0;
+    }
+    MultiReservation r;
+    if (!r.acquire(ngpu)) return 0;
+    if (n == 0) return 1;
+    if (!h_keys) return 0;
+    int P = std::min<int>((int)r.cs.size(), kDistMaxGpus);
+    // contiguous shards, starts 16-byte aligned; fewer GPUs when there are fewer keys than that
+    const size_t shard = (((n + P - 1) / P) + 3) & ~(size_t)3;
+    P = (int)((n + shard - 1) / shard);
+    if (shard >= ((size_t)1 << 30)) {
+        fprintf(stderr, "libsort: %zu keys over %d GPUs: shards must stay below 2^30 keys\n", n, P);
+        return 0;
+    }
+    auto &cs = r.cs;
+    auto shard_len = [&](int g) { return std::min(shard, n - (size_t)g * shard); };
+    if (P > 1 && !dist_enable_peers(std::vector<DeviceCtx *>(cs.begin(), cs.begin() + P))) return 0;
+
+    // 1. shards to the GPUs, a stratified sample of each
+    static std::atomic<uint32_t> seed{1};
+    const uint32_t sd = seed.fetch_add(1);
+    for (int g = 0; g < P; g++) {
+        DeviceCtx &c = *cs[g];
+        if (!cuda_ok(cudaSetDevice(c.dev), "cudaSetDevice")) return 0;
+        if (!ensure_capacity(c, shard + shard / 4, 0) || !dist_small_buffers(c, P, g == 0)) return 0;
+        if (!c.copier.to_device(c.a, h_keys + (size_t)g * shard, shard_len(g) * sizeof(uint32_t), c.stream)) return 0;
+        if (!cuda_ok(sample_keys(c.a, shard_len(g), c.small, kDistSamples, sd, c.stream), "sample")) return 0;
+        if (!cuda_ok(cudaMemcpyPeerAsync(cs[0]->gather + (size_t)g * kDistSamples, cs[0]->dev, c.small, c.dev,
+                                         kDistSamples * sizeof(uint32_t), c.stream),
+                     "cudaMemcpyPeerAsync(samples)"))
+            return 0;
+    }
+    if (!dist_sync_all(cs, P, "sync(samples)")) return 0;
+
+    // 2. splitters = quantiles of the sorted sample (GPU 0), handed to every GPU
+    uint32_t *splitters[kDistMaxGpus], *counts[kDistMaxGpus];
+    for (int g = 0; g < P; g++) {
+        splitters[g] = cs[g]->small + kDistSamples;
+        counts[g] = cs[g]->small + kDistSamples + 16;
+    }
+    {
+        DeviceCtx &c = *cs[0];
+        const size_t all = (size_t)P * kDistSamples;
+        if (!cuda_ok(cudaSetDevice(c.dev), "cudaSetDevice")) return 0;
+        uint32_t *res = nullptr;
+        if (!cuda_ok(sort_bits(c.gather, c.gather + all, c.gather + 2 * all, c.gather + all, all, 0, 32, nullptr,
+                               BOUNDS_EXACT, c.ws_small, c.ws_small_cap, c.stream, &res, nullptr),
+                     "sample sort"))
+            return 0;
+        if (!cuda_ok(pick_splitters(c.gather + all, all, P, splitters[0], c.stream), "pick splitters")) return 0;
+        for (int g = 1; g < P; g++)
+            if (!cuda_ok(cudaMemcpyPeerAsync(splitters[g], cs[g]->dev, splitters[0], c.dev, 16 * sizeof(uint32_t), c.stream),
+                         "cudaMemcpyPeerAsync(splitters)"))
+                return 0;
+        if (!cuda_ok(cudaStreamSynchronize(c.stream), "sync(splitters)")) return 0;
+    }
+
+    // 3. keys per destination on every GPU -> receive layout (sources in GPU order, no gaps)
+    uint32_t h_counts[kDistMaxGpus][16];
+    for (int g = 0; g < P; g++) {
+        DeviceCtx &c = *cs[g];
+        if (!cuda_ok(cudaSetDevice(c.dev), "cudaSetDevice")) return 0;
+        if (!cuda_ok(split_counts(c.a, shard_len(g), splitters[g], P - 1, counts[g], c.stream), "destination counts"))
+            return 0;
+        if (!cuda_ok(cudaMemcpyAsync(h_counts[g], counts[g], 16 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream),
+                     "cudaMemcpy(counts)"))
+            return 0;
+    }
+    if (!dist_sync_all(cs, P, "sync(counts)")) return 0;
+    size_t totals[kDistMaxGpus] = {}, offs[kDistMaxGpus][kDistMaxGpus];
+    for (int d = 0; d < P; d++)
+        for (int g = 0; g < P; g++) {
+            offs[g][d] = totals[d];
+            totals[d] += h_counts[g][d];
+        }
+    for (int d = 0; d < P; d++) {
+        if (totals[d] > UINT32_MAX) {
+            fprintf(stderr, "libsort: %zu keys fall into one GPU's range; the local sort is 32-bit\n", totals[d]);
+            return 0;
+        }
+        if (!cuda_ok(cudaSetDevice(cs[d]->dev), "cudaSetDevice")) return 0;
+        if (!dist_recv_buffer(*cs[d], totals[d])) return 0;
+    }
+
+    // 4. fused partition + exchange: each GPU stores its keys into its peers' receive buffers
+    for (int g = 0; g < P; g++) {
+        DeviceCtx &c = *cs[g];
+        unsigned long long ptrs[kDistMaxGpus];
+        for (int d = 0; d < P; d++) ptrs[d] = reinterpret_cast<unsigned long long>(cs[d]->recv + offs[g][d]);
+        if (!cuda_ok(cudaSetDevice(c.dev), "cudaSetDevice")) return 0;
+        if (!cuda_ok(scatter_by_splitters(c.a, shard_len(g), splitters[g], P - 1, ptrs, c.ws, c.ws_cap, c.stream),
+                     "partition + exchange"))
+            return 0;
+    }
+    if (!dist_sync_all(cs, P, "sync(exchange)")) return 0;  // every store has landed before anyone sorts
+
+    // 5. local sort of what arrived, straight back into the caller's array (GPU d owns the d-th value range)
+    size_t first = 0;
+    for (int d = 0; d < P; d++) {
+        DeviceCtx &c = *cs[d];
+        if (!cuda_ok(cudaSetDevice(c.dev), "cudaSetDevice")) return 0;
+        if (totals[d]) {
+            if (!ensure_capacity(c, totals[d], 0)) return 0;  // the shard in c.a is no longer needed
+            uint32_t *res = nullptr;
+            if (!cuda_ok(sort_bits(c.recv, c.a, c.b, nullptr, totals[d], 0, 32, nullptr, BOUNDS_EXACT, c.ws, c.ws_cap,
+                                   c.stream, &res, nullptr),
+                         "local sort"))
+                return 0;
+            if (!c.copier.to_host(h_keys + first, res, totals[d] * sizeof(uint32_t), c.stream)) return 0;
+        }
+        first += totals[d];
+    }
+    if (first != n) {
+        fprintf(stderr, "libsort: distributed sort lost keys (%zu of %zu arrived)\n", first, n);
+        return 0;
+    }
+    if (!dist_sync_all(cs, P, "sync(result)")) return 0;
+    return 1;
+}

@@ -15,6 +15,7 @@
 #include <vector>
 
 #include "libsort.h"
+#include "libsort_b200.h"  // additive: libsortDistribSort (every GPU of the box, exchange over NVLink)
 
 static inline uint32_t group_of(uint32_t v, int pos, int width) { return (v >> pos) & ((1u << width) - 1); }
 
@@ -87,13 +88,15 @@ static int run_tests(size_t n)
     std::vector<uint32_t> in(n);
     populateInput(in.data(), n);
     if (!check_partial(in, 0, 8)) { fprintf(stderr, "GPU partial test failed\n"); return 1; }
-    std::vector<uint32_t> gpu = in, cpu = in, dis = in;
+    std::vector<uint32_t> gpu = in, cpu = in, dis = in, nvl = in;
     if (!providedGpu(gpu.data(), n) || !ascending(gpu)) { fprintf(stderr, "GPU sort failed\n"); return 1; }
     if (!providedCpu(cpu.data(), n) || !ascending(cpu)) { fprintf(stderr, "CPU sort failed\n"); return 1; }
     if (!distrib_sort(dis, nullptr, nullptr) || !ascending(dis)) { fprintf(stderr, "distributed sort failed\n"); return 1; }
     if (gpu != cpu) { fprintf(stderr, "CPU and GPU results disagree\n"); return 1; }
     if (gpu != dis) { fprintf(stderr, "distributed and single-GPU results disagree\n"); return 1; }
-    printf("Success! (%zu keys: gpuPartial boundaries, providedGpu == providedCpu == distribSort)\n", n);
+    if (!libsortDistribSort(nvl.data(), n, 0)) { fprintf(stderr, "NVLink distributed sort failed\n"); return 1; }
+    if (gpu != nvl) { fprintf(stderr, "NVLink distributed and single-GPU results disagree\n"); return 1; }
+    printf("Success! (%zu keys: gpuPartial boundaries, providedGpu == providedCpu == distribSort == libsortDistribSort)\n", n);
     return 0;
 }
 
@@ -117,6 +120,9 @@ static int run_bench(size_t n)
         double p16 = ms_of([&] { gpuPartialProfile(work.data(), bounds.data(), n, 0, 16); });
         work = orig;
         double wk = 0, sh = 0, dt = ms_of([&] { distrib_sort(work, &wk, &sh); });
+        work = orig;
+        double nv = ms_of([&] { libsortDistribSort(work.data(), n, 0); });
+        if (rep) printf("libsortDistribSort (all GPUs, NVLink exchange): %.2f ms\n", nv);
         if (rep)
             printf("%.1f MiB through the host-pointer ABI (pageable memory):\n\tfull sort %.2f ms\n\tpartial 8b %.2f ms\n"
                    "\tpartial 16b %.2f ms\n\tdistribSort (2 partitions, 4x8b) %.2f ms (workers %.2f, shuffle %.2f)\n",

@@ -95,3 +95,16 @@ def sortPartial(buf: bytearray, offset, width):
     if not res:
         raise RuntimeError("Libsort had an internal error")
     return list(boundaries)
+
+
+def sortDistrib(buf: bytearray, ngpu=0):
+    """Sort buf (C uint32s) in place across `ngpu` GPUs of this box (0 = all of the pool):
+    shards exchanged GPU-to-GPU over NVLink instead of through the host shuffle of
+    reference sort.py:129-175 / benchmark/pkg/sort/distrib.go:183-248 (additive API)."""
+    nElem = int(len(buf) / 4)
+    if nElem == 0:
+        return
+    cRaw = (ctypes.c_uint8 * len(buf)).from_buffer(buf)
+    res = binding.lib().libsortDistribSort(ctypes.cast(cRaw, ctypes.c_void_p), ctypes.c_size_t(nElem), ctypes.c_int(ngpu))
+    if not res:
+        raise RuntimeError("Libsort had an internal error")

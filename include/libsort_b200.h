@@ -86,6 +86,21 @@ LIBSORT_API int libsortIpcExport(void *ptr, void *handle64);
 LIBSORT_API int libsortIpcOpen(const void *handle64, void **ptr);
 LIBSORT_API int libsortIpcClose(void *ptr);
 
+/*
+ * The whole distributed sort behind one call, for a caller that drives every
+ * GPU of the box from ONE process -- what the reference's Go benchmark driver
+ * does with its worker pool (benchmark/pkg/sort/distrib.go:183-248) and its C++
+ * twin with host threads (localTest/benchmarks.cpp:70-160).  h_keys (HOST,
+ * pinned or pageable) is cut into ngpu contiguous shards (ngpu <= 0: every GPU
+ * of the pool; at most 16), sampled, partitioned by value range and exchanged
+ * GPU-to-GPU over NVLink peer stores in one fused kernel per GPU, sorted locally
+ * and written back ascending into h_keys.  n may exceed 2^32 as long as every
+ * shard stays below 2^30 keys.  Blocks until every requested GPU is free, like
+ * the legacy calls.  Returns bool like them (1 = ok, 0 = failed, message on
+ * stderr).  Requires initLibSort() and peer access between the GPUs.
+ */
+LIBSORT_API int libsortDistribSort(uint32_t *h_keys, size_t n, int ngpu);
+
 /* populateInput at an explicit stream position: arr[i] = element first+i of the
  * fresh-process PCG sequence (reference libsort/utils.cu:63-79).  Thread safe. */
 LIBSORT_API void libsortPopulateInputAt(uint32_t *arr, size_t nelem, uint64_t first);

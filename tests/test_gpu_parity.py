@@ -254,3 +254,18 @@ def test_splitter_scatter_single_gpu(bulk):
     r = subprocess.run([sys.executable, os.path.join(os.path.dirname(__file__), "split_worker.py")], env=e,
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+@pytest.mark.parametrize("n", [0, 1, 3, 1000, (1 << 20) + 7, (1 << 24) + 5])
+def test_distrib_sort_host_call(gpu_lib, oracle, n):
+    """libsortDistribSort (the whole distributed sort behind one host-pointer call, every GPU the
+    pool has -- one on the driver's box, where it degenerates to partition-to-self + local sort)
+    against the oracle's full sort; the multi-GPU run is tools/gpu_multi.sh / tests/distrib_host_worker.py."""
+    k = oracle.pcg_stream(n).copy()
+    if n >= 1000:
+        k[::3] &= np.uint32(0x00FF00FF)            # duplicates + skew
+    want = oracle.full_sort(k)
+    got = k.copy()
+    assert gpu_lib.libsortDistribSort(got.ctypes.data, n, 0) == 1
+    assert np.array_equal(got, want)
+    assert gpu_lib.libsortDistribSort(got.ctypes.data, n, 99) == 0      # more GPUs than any pool has
