@@ -329,7 +329,7 @@ def main():
     ap.add_argument("--keys", type=int, default=N_PER_GPU, help="keys per GPU")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
                     help="multi-GPU key exchange: fused scatter into peer memory, or NCCL all-to-all")
-    ap.add_argument("--dist", default="uniform", choices=["uniform", "zipf", "consthigh", "consthigh16"],
+    ap.add_argument("--dist", default="uniform", choices=["uniform", "zipf", "consthigh", "consthigh16", "allequal", "halfdup"],
                     help="multi-GPU input distribution (BASELINE configs[4] skew cases)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

@@ -47,7 +47,7 @@ struct DeviceCtx {
     // single-process distributed sort (libsortDistribSort)
     uint32_t *recv = nullptr;   // keys arriving from every GPU
     size_t recv_cap = 0;
-    uint32_t *small = nullptr;  // samples | splitters | counts
+    uint32_t *small = nullptr;  // samples | splitters + tie thresholds (32 words) | counts
     uint32_t *gather = nullptr; // device 0: all samples | sorted | scratch
     size_t gather_cap = 0;
     void *ws_small = nullptr;
@@ -467,7 +467,7 @@ constexpr int kDistMaxGpus = 16;             // SplitBinner holds 15 splitters
 
 bool dist_small_buffers(DeviceCtx &c, int P, bool root)
 {
-    if (!c.small && !cuda_ok(cudaMalloc(&c.small, (kDistSamples + 32) * sizeof(uint32_t)), "cudaMalloc(samples)"))
+    if (!c.small && !cuda_ok(cudaMalloc(&c.small, (kDistSamples + 64) * sizeof(uint32_t)), "cudaMalloc(samples)"))
         return false;
     if (!root) return true;
     const size_t all = (size_t)P * kDistSamples;
@@ -580,7 +580,7 @@ API int libsortDistribSort(uint32_t *h_keys, size_t n, int ngpu)
     uint32_t *splitters[kDistMaxGpus], *counts[kDistMaxGpus];
     for (int g = 0; g < P; g++) {
         splitters[g] = cs[g]->small + kDistSamples;
-        counts[g] = cs[g]->small + kDistSamples + 16;
+        counts[g] = cs[g]->small + kDistSamples + 32;
     }
     {
         DeviceCtx &c = *cs[0];
@@ -593,7 +593,7 @@ API int libsortDistribSort(uint32_t *h_keys, size_t n, int ngpu)
             return 0;
         if (!cuda_ok(pick_splitters(c.gather + all, all, P, splitters[0], c.stream), "pick splitters")) return 0;
         for (int g = 1; g < P; g++)
-            if (!cuda_ok(cudaMemcpyPeerAsync(splitters[g], cs[g]->dev, splitters[0], c.dev, 16 * sizeof(uint32_t), c.stream),
+            if (!cuda_ok(cudaMemcpyPeerAsync(splitters[g], cs[g]->dev, splitters[0], c.dev, 32 * sizeof(uint32_t), c.stream),
                          "cudaMemcpyPeerAsync(splitters)"))
                 return 0;
         if (!cuda_ok(cudaStreamSynchronize(c.stream), "sync(splitters)")) return 0;

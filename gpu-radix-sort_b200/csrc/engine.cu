@@ -441,7 +441,7 @@ cudaError_t pick_splitters(const uint32_t *sorted, size_t nsorted, int nranks, u
 cudaError_t split_counts(const uint32_t *in, size_t n, const uint32_t *splitters, int nsplit, uint32_t *d_counts,
                          cudaStream_t st)
 {
-    if (nsplit < 0 || nsplit > MAX_SPLITTERS) return cudaErrorInvalidValue;
+    if (nsplit < 0 || nsplit > MAX_SPLITTERS || n > 0xffffffffull) return cudaErrorInvalidValue;
     DevInfo *dev = nullptr;
     CK(dev_info(&dev));
     CK(cudaMemsetAsync(d_counts, 0, (MAX_SPLITTERS + 1) * sizeof(uint32_t), st));

@@ -268,22 +268,43 @@ struct RadixBinner {
     {
         return __funnelshift_r(key, key, (shift + 30u) & 31u) & (mask << 2);
     }
+    // position-aware forms (SplitBinner splits ties by position; a digit does not care)
+    __device__ __forceinline__ uint32_t bin(uint32_t key, uint32_t) const { return bin(key); }
+    __device__ __forceinline__ uint32_t bin4(uint32_t key, uint32_t) const { return bin4(key); }
+    static constexpr bool kByPosition = false;  // bin is a function of the key alone
     __device__ __forceinline__ uint32_t pad_bin() const { return mask; }  // bin of the 0xffffffff padding keys
     __device__ __forceinline__ int nbits() const { return __popc(mask); }
 };
 constexpr int MAX_SPLITTERS = 15;
+constexpr int SPLIT_WORDS = 32;    // device splitter table: [0,16) values, [16,32) tie thresholds
+constexpr int SPLIT_TIE_OFFSET = 16;
 struct SplitArg { const uint32_t *d_splitters; int nsplit; };  // splitters live in device memory (no host round trip)
+// Position hash used to split ties: consecutive positions spread evenly over [0, 2^32).
+__device__ __forceinline__ uint32_t tie_hash(uint32_t idx) { return idx * 0x9E3779B1u; }
 // NS = compiled-in capacity (1, 3, 7 or 15 splitters for up to 2, 4, 8, 16 ranks):
 // only NS compares per key and NS registers.
+//
+// Ties: a key value that fills more than one rank's share appears as several equal
+// splitters.  Splitter j then carries a threshold T_j (ascending within the run of equal
+// splitters, 0 = "no tie splitting here"): a key EQUAL to splitter j counts as past it only
+// if tie_hash(position) >= T_j.  Keys-only sort, so which copy goes where does not matter;
+// the count kernel and the scatter kernel evaluate the same function of (key, position).
 template <int NS>
 struct SplitBinner {
     using Arg = SplitArg;
     uint32_t v[NS];
     int nsplit;
-    __device__ __forceinline__ explicit SplitBinner(const Arg &a) : nsplit(a.nsplit)
+    const uint32_t *table;
+    bool ties;
+    __device__ __forceinline__ explicit SplitBinner(const Arg &a) : nsplit(a.nsplit), table(a.d_splitters)
     {
+        uint32_t any = 0;
 #pragma unroll
-        for (int j = 0; j < NS; j++) v[j] = j < a.nsplit ? a.d_splitters[j] : 0xffffffffu;
+        for (int j = 0; j < NS; j++) {
+            v[j] = j < a.nsplit ? a.d_splitters[j] : 0xffffffffu;
+            any |= j < a.nsplit ? a.d_splitters[SPLIT_TIE_OFFSET + j] : 0u;
+        }
+        ties = any != 0;
     }
     // number of splitters <= key.  Unused slots hold 0xffffffff; the min() undoes what a key of
     // 0xffffffff would count against them.  NS >= 7: branch-free binary search (3 or 4 compares
@@ -315,6 +336,19 @@ struct SplitBinner {
         return min(d, (uint32_t)nsplit);
     }
     __device__ __forceinline__ uint32_t bin4(uint32_t key) const { return bin(key) << 2; }
+    // destination of the key at position idx of the shard: as bin(key), minus the equal splitters
+    // whose threshold the position's hash stays below (uniform branch: most inputs have no ties)
+    __device__ __forceinline__ uint32_t bin(uint32_t key, uint32_t idx) const
+    {
+        uint32_t d = bin(key);
+        if (ties) {  // (a splitter of 0xffffffff never has a threshold, so the padding keys stay in the last bin)
+            const uint32_t h = tie_hash(idx);
+            while (d > 0 && __ldg(table + d - 1) == key && h < __ldg(table + SPLIT_TIE_OFFSET + d - 1)) --d;
+        }
+        return d;
+    }
+    __device__ __forceinline__ uint32_t bin4(uint32_t key, uint32_t idx) const { return bin(key, idx) << 2; }
+    static constexpr bool kByPosition = true;  // equal keys may sit in different bins
     __device__ __forceinline__ uint32_t pad_bin() const { return (uint32_t)nsplit; }
     __device__ __forceinline__ int nbits() const { return 32 - __clz(nsplit); }  // bins 0..nsplit
 };
@@ -365,6 +399,7 @@ struct OnesweepSmem {
     uint32_t next_tile;
     BinnerArg binner_arg;  // copy for the out-of-line heavy-tile path
     uint32_t heavy_d4;  // 4 * (a digit holding more than a quarter of the current tile), valid when the tile votes heavy
+    uint32_t bucket_start[PTR_OUT ? MAX_SPLITTERS + 2 : 1];  // position-binned write-out (SplitBinner): bucket b starts here
 };
 
 constexpr int RANK_BALLOT = 0;  // one vote.ballot per digit bit + a leader atomic: architecturally ordered
@@ -388,6 +423,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
                uint32_t *__restrict__ ticket, uint32_t ntiles, int use_tma)
 {
     using Smem = OnesweepSmem<THREADS, KPT, PTR_OUT, typename Binner::Arg>;
+    static_assert(!(RANK == RANK_ATOMS && Binner::kByPosition), "the heavy-tile path bins by key alone");
     constexpr int TILE = Smem::TILE;
     constexpr int NWARPS = Smem::NWARPS;
     static_assert(THREADS >= RADIX, "need one thread per bin");
@@ -464,7 +500,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
 #pragma unroll
         //     (indexed with bin(), not bin4(): a different expression than (4) uses, so that the
         //     optimiser recomputes the address there instead of spilling KPT of them across barriers)
-        for (int i = 0; i < KPT; i++) atomicAdd(&s.warp_hist[warp][binner.bin(key[i])], 1u);
+        for (int i = 0; i < KPT; i++) atomicAdd(&s.warp_hist[warp][binner.bin(key[i], tile_base + wbase + i * 32)], 1u);
         __syncthreads();
 
         // (3) bin threads: reduce over warps, publish the tile aggregate,
@@ -507,7 +543,8 @@ __global__ void __launch_bounds__(THREADS, MINB)
             if (!heavy) {
 #pragma unroll
                 for (int i = 0; i < KPT; i++) {
-                    const uint32_t p4 = atomicAdd(reinterpret_cast<uint32_t *>(my_hist + binner.bin4(key[i])), 4u);
+                    const uint32_t p4 =
+                        atomicAdd(reinterpret_cast<uint32_t *>(my_hist + binner.bin4(key[i], tile_base + wbase + i * 32)), 4u);
                     *reinterpret_cast<uint32_t *>(tile_bytes + p4) = key[i];
                 }
             } else {
@@ -523,7 +560,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
             const uint32_t hist_addr = smem_u32(my_hist);
 #pragma unroll
             for (int i = 0; i < KPT; i++) {
-                const uint32_t d4 = binner.bin4(key[i]);
+                const uint32_t d4 = binner.bin4(key[i], tile_base + wbase + i * 32);
                 const uint32_t peers = match_digit<NBITS>(d4 >> 2, nbits);
                 const uint32_t before = __popc(peers & lt);
                 const int top = 31 - __clz(peers);  // highest peer lane leads; its `before` + 1 is the group size
@@ -560,6 +597,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
                 st_relaxed(&desc[(size_t)cur * RADIX + tid], DESC_INCL | (excl + my_count));
             }
             const uint32_t my_start = my_start4 >> 2;
+            if (PTR_OUT && Binner::kByPosition && tid <= MAX_SPLITTERS + 1) s.bucket_start[tid] = my_start;
             if (PTR_OUT) {
                 const unsigned long long gptr = static_cast<const unsigned long long *>(base_v)[tid];
                 s.tile_dst[tid] = gptr + 4ull * (unsigned long long)excl - 4ull * (unsigned long long)my_start;
@@ -591,7 +629,15 @@ __global__ void __launch_bounds__(THREADS, MINB)
 #pragma unroll
         for (int i = 0; i < KPT; i++) {
             const uint32_t p = tid + i * THREADS;
-            const uint32_t d4 = binner.bin4(key[i]);
+            uint32_t d4;
+            if (PTR_OUT && Binner::kByPosition) {
+                // equal keys may sit in different buckets: the bucket follows from the position
+                uint32_t d = 0;
+                for (uint32_t b = 1; b <= pad_bin; b++) d += s.bucket_start[b] <= p ? 1u : 0u;
+                d4 = d << 2;
+            } else {
+                d4 = binner.bin4(key[i]);
+            }
             if (valid == TILE || p < valid) {
                 if (PTR_OUT)
                     *reinterpret_cast<uint32_t *>(*reinterpret_cast<const unsigned long long *>(
@@ -663,15 +709,28 @@ __global__ void __launch_bounds__(1024, 1) k_dest_hist(const uint32_t *__restric
     if (head > n) head = n;
     const size_t nvec = (n - head) >> 2, tail0 = head + (nvec << 2);
     const size_t gtid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, gstride = (size_t)gridDim.x * blockDim.x;
-    if (gtid < head) atomicAdd(&cnt[binner.bin(in[gtid])][lane], 1u);
-    if (gtid < n - tail0) atomicAdd(&cnt[binner.bin(in[tail0 + gtid])][lane], 1u);
     const uint4 *vin = reinterpret_cast<const uint4 *>(in + head);
-    for (size_t i = gtid; i < nvec; i += gstride) {
-        const uint4 v = ld_stream_v4(vin + i);
-        atomicAdd(&cnt[binner.bin(v.x)][lane], 1u);
-        atomicAdd(&cnt[binner.bin(v.y)][lane], 1u);
-        atomicAdd(&cnt[binner.bin(v.z)][lane], 1u);
-        atomicAdd(&cnt[binner.bin(v.w)][lane], 1u);
+    if (!binner.ties) {  // the usual case, kept free of the tie walk so that the streaming loop stays tight
+        if (gtid < head) atomicAdd(&cnt[binner.bin(in[gtid])][lane], 1u);
+        if (gtid < n - tail0) atomicAdd(&cnt[binner.bin(in[tail0 + gtid])][lane], 1u);
+        for (size_t i = gtid; i < nvec; i += gstride) {
+            const uint4 v = ld_stream_v4(vin + i);
+            atomicAdd(&cnt[binner.bin(v.x)][lane], 1u);
+            atomicAdd(&cnt[binner.bin(v.y)][lane], 1u);
+            atomicAdd(&cnt[binner.bin(v.z)][lane], 1u);
+            atomicAdd(&cnt[binner.bin(v.w)][lane], 1u);
+        }
+    } else {  // ties are split by position (SplitBinner), exactly as the scatter will
+        if (gtid < head) atomicAdd(&cnt[binner.bin(in[gtid], (uint32_t)gtid)][lane], 1u);
+        if (gtid < n - tail0) atomicAdd(&cnt[binner.bin(in[tail0 + gtid], (uint32_t)(tail0 + gtid))][lane], 1u);
+        for (size_t i = gtid; i < nvec; i += gstride) {
+            const uint4 v = ld_stream_v4(vin + i);
+            const uint32_t p = (uint32_t)(head + (i << 2));
+            atomicAdd(&cnt[binner.bin(v.x, p)][lane], 1u);
+            atomicAdd(&cnt[binner.bin(v.y, p + 1)][lane], 1u);
+            atomicAdd(&cnt[binner.bin(v.z, p + 2)][lane], 1u);
+            atomicAdd(&cnt[binner.bin(v.w, p + 3)][lane], 1u);
+        }
     }
     __syncthreads();
     if (threadIdx.x <= (unsigned)binner.nsplit) {
@@ -681,12 +740,34 @@ __global__ void __launch_bounds__(1024, 1) k_dest_hist(const uint32_t *__restric
     }
 }
 
-// splitters[g] = the g/P quantile of the sorted all-rank sample.
+// splitters[g-1] = the g/P quantile of the sorted all-rank sample; splitters[16 + g-1] = its tie
+// threshold (see SplitBinner).  When the quantile falls inside a run [r0, r1) of >= TIE_MIN_RUN equal
+// samples -- a value heavy enough to matter -- the copies of that value are cut at the quantile too:
+// the fraction (q - r0) / (r1 - r0) of them stays below this splitter.
+constexpr uint32_t TIE_MIN_RUN = 8;
 __global__ void k_pick_splitters(const uint32_t *__restrict__ sorted, uint32_t nsorted, int nranks,
                                  uint32_t *__restrict__ splitters)
 {
     const int g = threadIdx.x + 1;
-    if (g < nranks) splitters[g - 1] = sorted[(unsigned long long)g * nsorted / nranks];
+    if (threadIdx.x < SPLIT_WORDS - SPLIT_TIE_OFFSET) splitters[SPLIT_TIE_OFFSET + threadIdx.x] = 0;
+    if (g >= nranks) return;
+    const uint32_t q = (uint32_t)((unsigned long long)g * nsorted / nranks);
+    const uint32_t v = sorted[q];
+    splitters[g - 1] = v;
+    uint32_t lo = 0, hi = q;  // r0 = first index holding v
+    while (lo < hi) {
+        const uint32_t mid = lo + ((hi - lo) >> 1);
+        if (sorted[mid] < v) lo = mid + 1; else hi = mid;
+    }
+    const uint32_t r0 = lo;
+    lo = q + 1, hi = nsorted;  // r1 = first index holding more than v
+    while (lo < hi) {
+        const uint32_t mid = lo + ((hi - lo) >> 1);
+        if (sorted[mid] <= v) lo = mid + 1; else hi = mid;
+    }
+    const uint32_t r1 = lo;
+    if (r1 - r0 >= TIE_MIN_RUN && q > r0 && v != 0xffffffffu)  // 0xffffffff pads partial tiles: never split
+        splitters[SPLIT_TIE_OFFSET + g - 1] = (uint32_t)((((unsigned long long)(q - r0)) << 32) / (r1 - r0));
 }
 
 __global__ void k_store_ptrs(const PtrTable t, unsigned long long *__restrict__ dst)

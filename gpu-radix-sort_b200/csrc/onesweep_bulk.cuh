@@ -51,6 +51,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
                     uint32_t *__restrict__ ticket, uint32_t ntiles, int use_tma)
 {
     using Smem = BulkSmem<THREADS, KPT, typename Binner::Arg>;
+    static_assert(!(RANK == RANK_ATOMS && Binner::kByPosition), "the heavy-tile path bins by key alone");
     constexpr int TILE = Smem::TILE;
     constexpr int NWARPS = Smem::NWARPS;
     static_assert(THREADS >= RADIX, "need one thread per bin");
@@ -122,7 +123,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
 
         // (2) early counts: per-warp digit histogram (see k_onesweep for the bin()/bin4() note)
 #pragma unroll
-        for (int i = 0; i < KPT; i++) atomicAdd(&s.warp_hist[warp][binner.bin(key[i])], 1u);
+        for (int i = 0; i < KPT; i++) atomicAdd(&s.warp_hist[warp][binner.bin(key[i], tile_base + wbase + i * 32)], 1u);
         __syncthreads();
 
         // (3) bin threads: reduce over warps, publish the tile aggregate, finish the
@@ -190,7 +191,8 @@ __global__ void __launch_bounds__(THREADS, MINB)
             if (!heavy) {
 #pragma unroll
                 for (int i = 0; i < KPT; i++) {
-                    const uint32_t p4 = atomicAdd(reinterpret_cast<uint32_t *>(my_hist + binner.bin4(key[i])), 4u);
+                    const uint32_t p4 =
+                        atomicAdd(reinterpret_cast<uint32_t *>(my_hist + binner.bin4(key[i], tile_base + wbase + i * 32)), 4u);
                     *reinterpret_cast<uint32_t *>(tile_bytes + p4) = key[i];
                 }
             } else {
@@ -205,7 +207,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
             const uint32_t hist_addr = smem_u32(my_hist);
 #pragma unroll
             for (int i = 0; i < KPT; i++) {
-                const uint32_t d4 = binner.bin4(key[i]);
+                const uint32_t d4 = binner.bin4(key[i], tile_base + wbase + i * 32);
                 const uint32_t peers = match_digit<0>(d4 >> 2, nbits);
                 const uint32_t before = __popc(peers & lt);
                 const int top = 31 - __clz(peers);  // highest peer lane leads; its `before` + 1 is the group size

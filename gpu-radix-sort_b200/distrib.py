@@ -17,9 +17,10 @@ single exchange:
 
 Rank r ends up with the r-th value range, ascending.  torch.distributed is the
 plumbing (collectives, rendezvous); all key movement and sorting on the GPU is
-libsort.so.  Equal keys always go to the same rank (no tie splitting yet), so a
-single value with more than N/P copies unbalances the output -- reported by
-verify() as `imbalance`.
+libsort.so.  A key value heavy enough to span a splitter has its copies cut
+between the neighbouring ranks by position (tie thresholds, see SplitBinner in
+csrc/kernels.cuh), so even an all-equal input balances; verify() reports
+`imbalance` = largest range / mean.
 """
 import ctypes
 
@@ -50,6 +51,10 @@ def shard_of_pcg_stream(rank, n, transform=None):
         t = _u32_to_i32((x & 0x00FFFFFF) | 0xAB000000)
     elif transform == "consthigh16":
         t = _u32_to_i32((x & 0xFFFF) | 0xABCD0000)
+    elif transform == "allequal":   # every key the same: ties must be cut between ranks
+        t = torch.full_like(t, 0x12345678)
+    elif transform == "halfdup":    # every other key is one value, the rest uniform
+        t = torch.where((x & 1) == 1, torch.full_like(t, 0x40000000), t)
     elif transform not in (None, "uniform"):
         raise ValueError(transform)
     return t.contiguous()
@@ -110,7 +115,7 @@ class DistributedSorter:
         self.samples_sorted = torch.empty_like(self.all_samples)
         self.samples_tmp = torch.empty_like(self.all_samples)
         self.ws_small = torch.empty(L.libsortWorkspaceBytes(S * self.world), dtype=torch.uint8, device=dev)
-        self.splitters = torch.zeros(16, dtype=i32, device=dev)
+        self.splitters = torch.zeros(32, dtype=i32, device=dev)   # 16 values + 16 tie thresholds
         self.counts = torch.zeros(16, dtype=i32, device=dev)
         self.count_matrix = torch.zeros(16 * self.world, dtype=i32, device=dev)
         self.token = torch.zeros(1, dtype=i32, device=dev)

@@ -11,21 +11,50 @@ import numpy as np
 MAX_RANKS = 16   # SplitBinner holds at most 15 splitters
 
 
-def choose_splitters(sorted_sample, world):
-    """world-1 ascending uint32 splitters: the g/world quantiles of a sorted sample.
-    (Mirrors k_pick_splitters on the device.)"""
+TIE_MIN_RUN = 8          # k_pick_splitters: runs of equal samples shorter than this are not split
+TIE_HASH = 0x9E3779B1    # tie_hash(position) = position * TIE_HASH mod 2^32
+
+
+def choose_splitters(sorted_sample, world, with_ties=False):
+    """world-1 ascending uint32 splitters: the g/world quantiles of a sorted sample
+    (mirrors k_pick_splitters on the device).  with_ties=True also returns the tie
+    thresholds: where quantile index q falls inside a run [r0, r1) of >= TIE_MIN_RUN
+    equal samples, threshold = floor((q - r0) * 2^32 / (r1 - r0)), else 0."""
     s = np.asarray(sorted_sample, dtype=np.uint32)
     if world < 1 or world > MAX_RANKS:
         raise ValueError("world size must be in 1..%d" % MAX_RANKS)
     if s.size == 0:
-        return np.zeros(world - 1, dtype=np.uint32)
-    idx = (np.arange(1, world, dtype=np.uint64) * np.uint64(s.size)) // np.uint64(world)
-    return s[idx.astype(np.int64)]
+        z = np.zeros(world - 1, dtype=np.uint32)
+        return (z, z.copy()) if with_ties else z
+    idx = ((np.arange(1, world, dtype=np.uint64) * np.uint64(s.size)) // np.uint64(world)).astype(np.int64)
+    spl = s[idx]
+    if not with_ties:
+        return spl
+    r0 = np.searchsorted(s, spl, side="left")
+    r1 = np.searchsorted(s, spl, side="right")
+    thr = np.zeros(world - 1, dtype=np.uint32)
+    for j in range(world - 1):
+        run, below = int(r1[j] - r0[j]), int(idx[j] - r0[j])
+        if run >= TIE_MIN_RUN and below > 0 and int(spl[j]) != 0xFFFFFFFF:
+            thr[j] = (below << 32) // run
+    return spl, thr
 
 
-def destination(keys, splitters):
-    """Destination rank of every key = number of splitters <= key (SplitBinner::bin)."""
-    return np.searchsorted(np.asarray(splitters, dtype=np.uint32), np.asarray(keys, dtype=np.uint32), side="right")
+def destination(keys, splitters, thresholds=None, positions=None):
+    """Destination rank of every key (SplitBinner::bin): the number of splitters s_j with
+    key > s_j, or key == s_j and tie_hash(position) >= threshold_j.  Without thresholds
+    that is the number of splitters <= key."""
+    k = np.asarray(keys, dtype=np.uint32)
+    spl = np.asarray(splitters, dtype=np.uint32)
+    if thresholds is None or not np.any(thresholds):
+        return np.searchsorted(spl, k, side="right")
+    thr = np.asarray(thresholds, dtype=np.uint32)
+    pos = np.arange(k.size, dtype=np.uint64) if positions is None else np.asarray(positions, dtype=np.uint64)
+    h = ((pos * np.uint64(TIE_HASH)) & np.uint64(0xFFFFFFFF)).astype(np.uint32)
+    d = np.zeros(k.size, dtype=np.int64)
+    for j in range(spl.size):
+        d += (k > spl[j]) | ((k == spl[j]) & (h >= thr[j]))
+    return d
 
 
 def recv_layout(count_matrix):

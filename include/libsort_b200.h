@@ -59,10 +59,16 @@ LIBSORT_API int libsortDeviceSort(const uint32_t *d_in, uint32_t *d_out, uint32_
  * torch.distributed; see gpu-radix-sort_b200/distrib.py.
  *
  * libsortDeviceSample:        nsamples stratified pseudo-random keys of the shard.
- * libsortDevicePickSplitters: d_splitters[g-1] = g/nranks quantile of a sorted sample.
- * libsortDeviceSplitCounts:   d_counts[0..nsplit] (16 words) = keys per
- *     destination; destination of a key = number of splitters <= key
- *     (splitters: DEVICE array, ascending, nsplit <= 15).
+ * The splitter table is a DEVICE array of LIBSORT_SPLIT_WORDS (32) words: [0, 16) the
+ *     splitter values (ascending, nsplit <= 15 used), [16, 32) their tie thresholds.
+ *     Destination of the key at position i of the shard = number of splitters s_j with
+ *     key > s_j, or key == s_j and (i * 0x9E3779B1 mod 2^32) >= threshold_j.  With all
+ *     thresholds 0 that is "number of splitters <= key"; non-zero thresholds cut the copies
+ *     of a heavily repeated key value between neighbouring ranks (keys-only sort, so any
+ *     copy may go anywhere in the value's range) -- even an all-equal input balances.
+ * libsortDevicePickSplitters: d_splitters[g-1] = g/nranks quantile of a sorted sample;
+ *     thresholds from where the quantile falls inside a run of >= 8 equal samples.
+ * libsortDeviceSplitCounts:   d_counts[0..nsplit] (16 words) = keys per destination.
  * libsortDeviceScatterToPeers: stable partition by destination written straight
  *     to dest_ptrs[0..nsplit] (splitters: DEVICE array; dest_ptrs: HOST array of device addresses, local or
  *     cudaIpc/NVLink-mapped peer memory): partition + key exchange in one
@@ -71,6 +77,8 @@ LIBSORT_API int libsortDeviceSort(const uint32_t *d_in, uint32_t *d_out, uint32_
  *     handles) so ranks in different processes can map each other's receive
  *     buffers.
  */
+#define LIBSORT_SPLIT_WORDS 32
+#define LIBSORT_SPLIT_TIE_OFFSET 16
 LIBSORT_API int libsortDeviceSample(const uint32_t *d_in, size_t n, uint32_t *d_out, uint32_t nsamples, uint32_t seed,
                                     void *stream);
 LIBSORT_API int libsortDevicePickSplitters(const uint32_t *d_sorted, size_t nsorted, int nranks, uint32_t *d_splitters,

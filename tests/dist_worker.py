@@ -23,6 +23,8 @@ def shard(rank, n, kind):
         x = (np.floor(2.0 ** (32.0 * x.astype(np.float64) / 2.0 ** 32)) - 1).astype(np.uint32)
     elif kind == "fewvalues":
         x = (x % np.uint32(5)).astype(np.uint32) * np.uint32(1000)
+    elif kind == "allequal":
+        x = np.full(x.size, 0x12345678, np.uint32)
     return x
 
 
@@ -32,13 +34,13 @@ def main():
     if mode == "gloo":
         dist.init_process_group("gloo")
         rank, world = dist.get_rank(), dist.get_world_size()
-        for kind in ("uniform", "consthigh", "zipf", "fewvalues"):
+        for kind in ("uniform", "consthigh", "zipf", "fewvalues", "allequal"):
             keys = shard(rank, n, kind)
             sample = torch.from_numpy(keys[:: max(1, n // 256)][:256].astype(np.int64))
             gathered = [torch.empty_like(sample) for _ in range(world)]
             dist.all_gather(gathered, sample)
-            spl = plan.choose_splitters(np.sort(torch.cat(gathered).numpy().astype(np.uint32)), world)
-            dest = plan.destination(keys, spl)
+            spl, thr = plan.choose_splitters(np.sort(torch.cat(gathered).numpy().astype(np.uint32)), world, with_ties=True)
+            dest = plan.destination(keys, spl, thr)          # ties cut by position in the shard
             cnt = torch.from_numpy(np.bincount(dest, minlength=world).astype(np.int64))
             rows = [torch.empty_like(cnt) for _ in range(world)]
             dist.all_gather(rows, cnt)
@@ -57,6 +59,8 @@ def main():
             allkeys = np.sort(np.concatenate([shard(r, n, kind) for r in range(world)]))
             start = int(totals[:rank].sum())
             assert np.array_equal(mine, allkeys[start:start + mine.size]), kind
+            if kind in ("fewvalues", "allequal"):
+                assert plan.imbalance(totals) < 1.1, (kind, totals)
         print("rank %d gloo plan ok" % rank)
     else:
         local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -67,7 +71,7 @@ def main():
         distrib = importlib.import_module("gpu-radix-sort_b200.distrib")
         for exch in ("p2p", "nccl"):
             sorter = distrib.DistributedSorter(n, mode=exch, slack=2.5)
-            for kind in ("uniform", "consthigh", "zipf"):
+            for kind in ("uniform", "consthigh", "zipf", "fewvalues", "allequal"):
                 keys = shard(rank, n, kind)
                 d = torch.from_numpy(keys.view(np.int32)).cuda()
                 for rep in range(2):
@@ -77,6 +81,8 @@ def main():
                 start = int(sum(stats["keys_per_rank"][:rank]))
                 got = out.cpu().numpy().view(np.uint32)
                 assert np.array_equal(got, allkeys[start:start + cnt]), (exch, kind)
+                if kind in ("fewvalues", "allequal"):
+                    assert stats["imbalance"] < 1.1, (kind, stats)
                 if rank == 0:
                     print(exch, kind, "ok; keys/rank", stats["keys_per_rank"], "imbalance %.3f" % stats["imbalance"])
             sorter.close()

@@ -30,6 +30,12 @@ def main():
     assert L.libsortDistribSort(got.ctypes.data, n, 0) == 1
     assert np.array_equal(got, np.sort(k)), "small distributed sort differs from numpy"
     res["exact_small"] = True
+    # heavy duplicates: one value in half of the keys, then every key equal (ties are cut between GPUs)
+    for name, kk in (("halfdup", np.where(k & 1, np.uint32(0x40000000), k).astype(np.uint32)), ("allequal", np.full(n, 99, np.uint32))):
+        got = kk.copy()
+        assert L.libsortDistribSort(got.ctypes.data, n, 0) == 1
+        assert np.array_equal(got, np.sort(kk)), name
+    res["exact_duplicates"] = True
     # full size, pinned host memory
     n = (1 << lg) * P
     h = torch.empty(n, dtype=torch.int32).pin_memory()

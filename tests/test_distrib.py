@@ -25,6 +25,21 @@ def test_plan_functions(pkg):
     assert spl.tolist() == [250, 500, 750]
     d = plan.destination(np.array([0, 249, 250, 999, 500], np.uint32), spl)
     assert d.tolist() == [0, 0, 1, 3, 2]          # a key equal to a splitter goes right (SplitBinner::bin)
+    # ties: a value spanning several quantiles is cut by position; all-equal input balances
+    same = np.full(4000, 7, np.uint32)
+    spl, thr = plan.choose_splitters(same, 4, with_ties=True)
+    assert spl.tolist() == [7, 7, 7] and thr.tolist() == [1 << 30, 1 << 31, 3 << 30]
+    d = plan.destination(same, spl, thr)
+    assert np.abs(np.bincount(d, minlength=4) - 1000).max() <= 2          # low-discrepancy position hash
+    mixed = np.sort(np.concatenate([np.arange(100, dtype=np.uint32), np.full(700, 100, np.uint32),
+                                    np.arange(101, 301, dtype=np.uint32)]))
+    spl, thr = plan.choose_splitters(mixed, 4, with_ties=True)
+    assert spl.tolist() == [100, 100, 100] and thr[0] > 0
+    d = plan.destination(mixed, spl, thr)
+    assert np.all(np.diff(np.array([mixed[d == r].max() for r in range(4)]).astype(np.int64)) >= 0)   # ranges stay ordered
+    assert np.bincount(d, minlength=4).max() <= 260                                                   # and balanced
+    spl, thr = plan.choose_splitters(np.arange(1000, dtype=np.uint32), 4, with_ties=True)
+    assert thr.tolist() == [0, 0, 0]                                                                  # no ties, no thresholds
     off, tot = plan.recv_layout([[1, 2], [3, 4]])
     assert off.tolist() == [[0, 0], [1, 2]] and tot.tolist() == [4, 6]
     assert plan.imbalance([4, 6]) == pytest.approx(1.2)
@@ -48,4 +63,4 @@ def test_distributed_sort_on_gpus():
     world = 2 if ndev < 4 else 4
     r = torchrun(world, 29741, "nccl", 300000, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
-    assert r.stdout.count(" ok; keys/rank") == 6
+    assert r.stdout.count(" ok; keys/rank") == 10
