@@ -1,11 +1,13 @@
-"""The one data helper on the hot path (reference faasTest/pylibsort/data.py:313-317).
-
-The reference's file-backed distributed arrays (data.py:1-309) are FaaS
-exchange plumbing and out of scope.
+"""Data side of the reference's ``pylibsort`` (faasTest/pylibsort/data.py): the file-backed
+distributed arrays and request helpers live in ``distrib_array`` (pure Python, importable without a
+GPU) and are re-exported here under the reference's names; ``generateInputs`` is the one helper that
+calls into libsort (data.py:313-317).
 """
 import ctypes
 
 from .. import binding
+from ..distrib_array import (ArrayShape, DistribArray, DistribArrayError, SetDistribMount, closeOpenArrays,  # noqa: F401
+                             fileDistribArray, getOutputArray, getPartRefs, openArrs, partRef, readPartRefs, writeOutput)
 
 
 def generateInputs(n):

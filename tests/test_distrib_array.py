@@ -1,0 +1,177 @@
+"""File distributed arrays and the sort-request plumbing.  The CPU tests follow the
+reference's own plan for this layer (faasTest/testPyLibSort.py:35-199: partitions, whole-array I/O,
+reopen/destroy, partRefs, request parsing) plus the on-disk format itself; the GPU test runs the FaaS
+worker end to end (faasTest/f.py selfTest)."""
+import importlib
+import json
+import os
+import random
+
+import numpy as np
+import pytest
+
+
+@pytest.fixture()
+def da(pkg):
+    return importlib.import_module(pkg.__name__ + ".distrib_array")
+
+
+def fill(arr, szs=None):
+    szs = arr.shape.caps if szs is None else szs
+    bufs = []
+    for p in range(arr.shape.npart):
+        b = bytes(random.getrandbits(8) for _ in range(szs[p]))
+        arr.WritePart(p, b)
+        bufs.append(b)
+    return bufs
+
+
+def test_shape(da):
+    s = da.ArrayShape.fromUniform(40, 3)
+    assert (s.caps, s.lens, s.npart, s.starts) == ([40, 40, 40], [0, 0, 0], 3, [0, 40, 80, 120])
+    s = da.ArrayShape.fromCaps([8, 0, 12])
+    assert s.starts == [0, 8, 8, 20] and s.lens == [0, 0, 0]
+
+
+def test_partitions_and_whole_array(da, tmp_path):
+    shape = da.ArrayShape.fromUniform(40, 2)
+    arr = da.fileDistribArray.Create(tmp_path / "partTest0", shape)
+    first = fill(arr, [20, 20])
+    assert arr.ReadPart(0) == first[0]
+    assert arr.ReadPart(0, start=4, nbyte=4) == first[0][4:8]
+    more = fill(arr, [20, 20])                                     # appends
+    assert arr.ReadPart(0) == first[0] + more[0]
+    whole = first[0] + more[0] + first[1] + more[1]
+    assert arr.ReadAll() == whole
+    with pytest.raises(da.DistribArrayError, match="Wrote beyond end of partition"):
+        arr.WritePart(0, b"x")
+    with pytest.raises(da.DistribArrayError, match="Read beyond end of partition"):
+        arr.ReadPart(1, start=30, nbyte=20)
+    other = da.fileDistribArray.Create(tmp_path / "partTest1", shape)
+    other.WriteAll(whole)
+    assert other.ReadAll() == whole and other.shape.lens == [40, 40]
+    with pytest.raises(da.DistribArrayError, match="does not match array capacity"):
+        other.WriteAll(whole[:-1])
+    dest = bytearray(12)                                            # read into a caller's buffer
+    assert other.ReadPart(1, start=8, nbyte=12, dest=dest) is None and dest == whole[48:60]
+
+
+def test_on_disk_format(da, tmp_path):
+    """meta.json = {"Lens", "Caps"} in bytes; data.dat = partitions at their capacity offsets (file.go:36-41)."""
+    arr = da.fileDistribArray.Create(tmp_path / "fmt", da.ArrayShape.fromCaps([16, 8, 24]))
+    arr.WritePart(0, b"A" * 10)
+    arr.WritePart(2, b"C" * 24)
+    arr.WritePart(1, b"B" * 3)
+    arr.Close()
+    arr.Close()                                                     # idempotent
+    assert json.load(open(tmp_path / "fmt" / "meta.json")) == {"Lens": [10, 3, 24], "Caps": [16, 8, 24]}
+    raw = open(tmp_path / "fmt" / "data.dat", "rb").read()
+    assert len(raw) == 48 and raw[:10] == b"A" * 10 and raw[16:19] == b"B" * 3 and raw[24:] == b"C" * 24
+    # an array written by "the other side" (hand-made files) opens here; a short data file reads as zeros
+    os.mkdir(tmp_path / "foreign")
+    json.dump({"Lens": [4, 4], "Caps": [8, 8]}, open(tmp_path / "foreign" / "meta.json", "w"))
+    open(tmp_path / "foreign" / "data.dat", "wb").write(b"abcd\0\0\0\0wxyz")
+    f = da.fileDistribArray.Open(tmp_path / "foreign")
+    assert f.ReadPart(0) == b"abcd" and f.ReadPart(1) == b"wxyz" and bytes(f.ReadAll()) == b"abcd\0\0\0\0wxyz\0\0\0\0"
+
+
+def test_reopen_and_destroy(da, tmp_path):
+    shape = da.ArrayShape.fromUniform(10, 2)
+    arr = da.fileDistribArray.Create(tmp_path / "distribArrayTest", shape)
+    assert arr.shape.npart == 2
+    bufs = fill(arr)
+    arr.Close()
+    again = da.fileDistribArray.Open(tmp_path / "distribArrayTest")
+    assert again.shape.caps == shape.caps and [again.ReadPart(p) for p in range(2)] == bufs
+    with pytest.raises(FileExistsError):
+        da.fileDistribArray.Create(tmp_path / "distribArrayTest", shape)
+    again.Destroy()
+    with pytest.raises(da.DistribArrayError, match="does not exist"):
+        da.fileDistribArray.Open(tmp_path / "distribArrayTest")
+
+
+def test_part_refs_and_requests(da, tmp_path):
+    da.SetDistribMount(tmp_path)
+    arr = da.fileDistribArray.Create(tmp_path / "distribArrayTest", da.ArrayShape.fromUniform(10, 2))
+    bufs = fill(arr)
+    assert da.partRef(arr, partID=0, start=0, nbyte=5).read() == bufs[0][:5]
+    assert da.partRef(arr, partID=1, start=2, nbyte=6).read() == bufs[1][2:8]
+    arr.Close()
+    req = {"offset": 0, "width": 2, "arrType": "file",
+           "input": [{"arrayName": "distribArrayTest", "partID": 0, "start": 0, "nbyte": 5},
+                     {"arrayName": "distribArrayTest", "partID": 1, "start": 2, "nbyte": 6},
+                     {"arrayName": "distribArrayTest", "partID": 1, "start": 4, "nbyte": -1}]}
+    refs = da.getPartRefs(req)
+    assert [r.read() for r in refs] == [bufs[0][:5], bufs[1][2:8], bufs[1][4:]]
+    assert bytes(da.readPartRefs(refs)) == bufs[0][:5] + bufs[1][2:8] + bufs[1][4:]
+    pinned_like = bytearray(32)
+    view = da.readPartRefs(refs, dest=pinned_like)
+    assert len(view) == 17 and bytes(pinned_like[:17]) == bytes(view)
+    with pytest.raises(ValueError, match="Invalid request type"):
+        da.getPartRefs(dict(req, arrType="redis"))
+    da.closeOpenArrays()
+
+
+def test_write_output_buckets(da, tmp_path):
+    """One output partition per bucket, sized by the boundaries (element indices -> bytes; data.py:289-298)."""
+    da.SetDistribMount(tmp_path)
+    keys = np.array([0, 0, 1, 3, 3, 3], dtype=np.uint32)            # sorted by a 2-bit group; group 2 is empty
+    da.writeOutput({"arrType": "file", "output": "out"}, keys.tobytes(), [0, 2, 3, 3])
+    out = da.fileDistribArray.Open(tmp_path / "out")
+    assert out.shape.caps == [8, 4, 0, 12] and out.shape.lens == out.shape.caps
+    assert [np.frombuffer(bytes(out.ReadPart(p)), np.uint32).tolist() for p in range(4)] == [[0, 0], [1], [], [3, 3, 3]]
+    out.Destroy()
+
+
+@pytest.mark.gpu
+def test_faas_worker_end_to_end(pkg, tmp_path):
+    """The reference's f.py selfTest flow: arrays on disk -> JSON request -> GPU partial sort -> bucket
+    partitions on disk, checked with checkPartial; then the error replies of the protocol."""
+    faas = importlib.import_module(pkg.__name__ + ".faas")
+    for n, off, w in ((1 << 20, 0, 8), (4096, 8, 4), (1 << 18, 16, 16)):
+        assert faas.selfTest(n, offset=off, width=w, mount=str(tmp_path)) == {"success": True, "err": ""}
+    assert faas.f({"arrType": "redis"})["success"] is False
+    pls = importlib.import_module(pkg.__name__ + ".pylibsort")
+    pls.SetDistribMount(tmp_path)
+    r = faas.f({"offset": 0, "width": 8, "arrType": "file", "output": "o",
+                "input": [{"arrayName": "missing", "partID": 0, "start": 0, "nbyte": -1}]})
+    assert r["success"] is False and "does not exist" in r["err"]
+
+
+def _invoke(pkg, stdin, env_extra):
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(pkg.__file__)))
+    env = dict(os.environ)
+    env.pop("OL_SHARED_VOLUME", None)
+    env.update(env_extra)
+    return subprocess.run([sys.executable, "-m", pkg.__name__ + ".faas"], input=stdin, capture_output=True, text=True,
+                          cwd=root, env=env, timeout=300)
+
+
+def test_direct_invoke_argument_errors(pkg, tmp_path):
+    """directInvoke() replies in JSON and exits 1 on a missing mount or a malformed request (f.py:162-174)."""
+    r = _invoke(pkg, "{}", {})
+    assert r.returncode == 1 and "OL_SHARED_VOLUME not set" in json.loads(r.stdout.strip().splitlines()[-1])["err"]
+    r = _invoke(pkg, "not json", {"OL_SHARED_VOLUME": str(tmp_path)})
+    assert r.returncode == 1 and "Argument parsing error" in json.loads(r.stdout.strip().splitlines()[-1])["err"]
+
+
+@pytest.mark.gpu
+def test_direct_invoke_sorts_request(pkg, da, tmp_path):
+    """The worker as a process: request on stdin, arrays under OL_SHARED_VOLUME, reply on stdout, exit 0."""
+    keys = np.random.default_rng(5).integers(0, 1 << 32, 50000, dtype=np.uint64).astype(np.uint32)
+    arr = da.fileDistribArray.Create(tmp_path / "in0", da.ArrayShape.fromUniform(100000, 2))
+    arr.WriteAll(keys.tobytes())
+    arr.Close()
+    req = {"offset": 8, "width": 8, "arrType": "file", "output": "out0",
+           "input": [{"arrayName": "in0", "partID": 1, "start": 0, "nbyte": -1},
+                     {"arrayName": "in0", "partID": 0, "start": 40, "nbyte": 60000}]}
+    r = _invoke(pkg, json.dumps(req), {"OL_SHARED_VOLUME": str(tmp_path)})
+    assert r.returncode == 0 and json.loads(r.stdout.strip().splitlines()[-1]) == {"success": True, "err": ""}, r.stdout + r.stderr
+    fed = np.concatenate([keys[25000:], keys[10:15010]])
+    out = da.fileDistribArray.Open(tmp_path / "out0")
+    got = np.frombuffer(bytes(out.ReadAll()), np.uint32)
+    order = np.argsort((fed >> 8) & 0xFF, kind="stable")
+    assert np.array_equal(got, fed[order])                            # stable partial sort of exactly the requested slices
+    assert out.shape.caps == (np.bincount((fed >> 8) & 0xFF, minlength=256) * 4).tolist()
