@@ -272,6 +272,9 @@ def run_multi(args, rank, world, local_rank):
     # one continuous PCG stream; rank g owns elements [g*n, (g+1)*n)  
     d_in = distrib.shard_of_pcg_stream(rank, n, args.dist)
     sorter = distrib.DistributedSorter(n, dist.group.WORLD, mode=args.exchange)
+    if args.algo == "stepwise":
+        run_multi_stepwise(args, rank, world, local_rank, sorter, d_in)
+        return
     for _ in range(max(args.warmup, 3)):
         sorter.sort(d_in)
     torch.cuda.synchronize()
@@ -320,6 +323,69 @@ def run_multi(args, rank, world, local_rank):
     dist.destroy_process_group()
 
 
+def run_multi_stepwise(args, rank, world, local_rank, sorter, d_in):
+    """--algo stepwise: the reference's own distributed algorithm (one exchange per 8-bit step) on the
+    NVLink backend, beside the default single-exchange sort -- the like-for-like number."""
+    import torch
+    import torch.distributed as dist
+    n = d_in.numel()
+    for _ in range(max(args.warmup, 3)):
+        sorter.sort_stepwise(d_in)
+    torch.cuda.synchronize()
+    dist.barrier()
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        out, cnt = sorter.sort_stepwise(d_in)
+    e1.record()
+    torch.cuda.synchronize()
+    dist.barrier()
+    ms_local = torch.tensor([e0.elapsed_time(e1) / args.steps], device="cuda")
+    dist.all_reduce(ms_local, op=dist.ReduceOp.MAX)
+    ms = float(ms_local.item())
+    clk = clocks.stop()
+    stats = sorter.verify(d_in, out, cnt)
+    marks = []
+
+    def ev(name):
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        marks.append((name, e))
+    dist.barrier()
+    torch.cuda.synchronize()
+    ev("start")
+    sorter.sort_stepwise(d_in, ev=ev)
+    torch.cuda.synchronize()
+    vals = torch.tensor([marks[i][1].elapsed_time(marks[i + 1][1]) for i in range(len(marks) - 1)], dtype=torch.float64,
+                        device="cuda")
+    dist.all_reduce(vals, op=dist.ReduceOp.MAX)
+    phases = {m[0] + "_ms": float(v) for m, v in zip(marks[1:], vals.tolist())}
+    if rank == 0:
+        total = n * world
+        step_bytes = 4.0 * n * (world - 1) / world          # uniform digits: (P-1)/P of a slice leaves the GPU per step
+        step_ms = sum(phases.values()) / max(len(phases), 1)
+        line = {
+            "metric": METRIC, "value": total / (ms * 1e-3) / 1e9, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+            "config": {"workload": "step-wise distributed LSD sort (reference distribSort protocol, 4 x 8-bit steps), 2^28 keys per GPU",
+                       "keys_per_gpu": n, "keys_total": total, "exchange": "p2p", "distribution": args.dist, "algo": "stepwise",
+                       "parallelism": "equal slices, 1 rank/GPU, one global counting sort per digit, stores into peer slices",
+                       "l2": "1 GiB slice per step per GPU, larger than L2"},
+            "clocks": clk, "verify": stats, "phases_ms": phases,
+            "gpu_launches": sorter.launches_per_stepwise_sort * args.steps,
+            "nvlink": {"bytes_out_per_gpu_per_step": step_bytes, "step_ms": step_ms,
+                       "gbs_per_direction": step_bytes / (step_ms * 1e-3) / 1e9 if step_ms else None, "peak_gbs": 770.0,
+                       "peak_source": "measured peer copy per direction (B200_PROFILING.md)"},
+        }
+        print(json.dumps(line), flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -331,6 +397,8 @@ def main():
                     help="multi-GPU key exchange: fused scatter into peer memory, or NCCL all-to-all")
     ap.add_argument("--dist", default="uniform", choices=["uniform", "zipf", "consthigh", "consthigh16", "allequal", "halfdup"],
                     help="multi-GPU input distribution (BASELINE configs[4] skew cases)")
+    ap.add_argument("--algo", default="samplesort", choices=["samplesort", "stepwise"],
+                    help="multi-GPU algorithm: one exchange by sampled splitters (default), or the reference's step-wise LSD protocol")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -12,7 +12,8 @@ LEGACY_SYMBOLS = ["initLibSort", "gpuPartial", "providedGpu", "providedCpu", "po
 ADDITIVE_SYMBOLS = ["libsortTileKeys", "libsortWorkspaceBytes", "libsortDeviceSort", "libsortDeviceCount",
                     "libsortReleaseCaches", "libsortErrorString", "libsortDebugSetPortionTiles",
                     "libsortDeviceSample", "libsortDevicePickSplitters", "libsortDeviceSplitCounts", "libsortPopulateInputAt", "libsortDeviceScatterToPeers",
-                    "libsortIpcAlloc", "libsortIpcFree", "libsortIpcExport", "libsortIpcOpen", "libsortIpcClose", "libsortDistribSort"]
+                    "libsortIpcAlloc", "libsortIpcFree", "libsortIpcExport", "libsortIpcOpen", "libsortIpcClose", "libsortDistribSort",
+                    "libsortStepTableBytes", "libsortStepTableInit", "libsortStepCounts", "libsortStepBases", "libsortStepScatter"]
 
 BOUNDS_REFERENCE = 0
 BOUNDS_EXACT = 1
@@ -98,6 +99,14 @@ def lib():
         getattr(L, name).restype = ci
     L.libsortDistribSort.argtypes = [vp, sz, ci]
     L.libsortDistribSort.restype = ci
+    L.libsortStepTableBytes.argtypes = []
+    L.libsortStepTableBytes.restype = sz
+    L.libsortStepTableInit.argtypes = [vp, vp, vp, ci, vp]
+    L.libsortStepCounts.argtypes = [vp, sz, ctypes.c_uint32, ctypes.c_uint32, vp, vp]
+    L.libsortStepBases.argtypes = [vp, ci, ci, vp, vp]
+    L.libsortStepScatter.argtypes = [vp, sz, ctypes.c_uint32, ctypes.c_uint32, vp, vp, sz, vp]
+    for name in ("libsortStepTableInit", "libsortStepCounts", "libsortStepBases", "libsortStepScatter"):
+        getattr(L, name).restype = ci
     _lib = L
     return L
 

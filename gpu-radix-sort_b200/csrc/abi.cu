@@ -661,3 +661,24 @@ API int libsortDistribSort(uint32_t *h_keys, size_t n, int ngpu)
     if (!dist_sync_all(cs, P, "sync(result)")) return 0;
     return 1;
 }
+
+// ---- step-wise distributed LSD sort: device building blocks (include/libsort_b200.h) ----
+API size_t libsortStepTableBytes(void) { return step_table_bytes(); }
+API int libsortStepTableInit(void *d_table, const unsigned long long *peers, const unsigned long long *slice_starts,
+                             int nslice, void *stream)
+{
+    return (int)step_table_init(d_table, peers, slice_starts, nslice, (cudaStream_t)stream);
+}
+API int libsortStepCounts(const uint32_t *d_in, size_t n, uint32_t shift, uint32_t nbits, uint32_t *d_counts, void *stream)
+{
+    return (int)step_counts(d_in, n, shift, nbits, d_counts, (cudaStream_t)stream);
+}
+API int libsortStepBases(const uint32_t *d_gathered, int nranks, int me, void *d_table, void *stream)
+{
+    return (int)step_bases(d_gathered, nranks, me, d_table, (cudaStream_t)stream);
+}
+API int libsortStepScatter(const uint32_t *d_in, size_t n, uint32_t shift, uint32_t nbits, const void *d_table,
+                           void *d_workspace, size_t workspace_len, void *stream)
+{
+    return (int)step_scatter(d_in, n, shift, nbits, d_table, d_workspace, workspace_len, (cudaStream_t)stream);
+}

@@ -5,6 +5,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <cstddef>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -59,6 +60,11 @@ using SmemBulk = BulkSmem<SORT_THREADS, SORT_KPT, RadixBinner::Arg>;
 using SmemSplitBulk = BulkSmem<SORT_THREADS, BALLOT_KPT, SplitArg>;
 #define KERNEL_B(NBITS) k_onesweep<SORT_THREADS, BALLOT_KPT, BALLOT_MINB, RANK_BALLOT, NBITS, SORT_LB, RadixBinner, false>
 #define KERNEL_SPLIT(NS) k_onesweep<SORT_THREADS, BALLOT_KPT, SPLIT_MINB, RANK_BALLOT, 0, SORT_LB, SplitBinner<NS>, true>
+// the radix scatter writing into an array sliced over several GPUs (step-wise distributed LSD sort)
+#define KERNEL_SLICED_A k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, RANK_ATOMS, 0, SORT_LB, RadixBinner, OUT_SLICED>
+#define KERNEL_SLICED_B k_onesweep<SORT_THREADS, BALLOT_KPT, SPLIT_MINB, RANK_BALLOT, 0, SORT_LB, RadixBinner, OUT_SLICED>
+using SmemSlicedA = OnesweepSmem<SORT_THREADS, SORT_KPT, OUT_SLICED, RadixBinner::Arg>;
+using SmemSlicedB = OnesweepSmem<SORT_THREADS, BALLOT_KPT, OUT_SLICED, RadixBinner::Arg>;
 
 
 
@@ -90,6 +96,7 @@ struct DevInfo {
     bool ready = false;
     int sms = 0;
     int occ_a = 0, occ_b = 0, occ_split = 0, occ_bulk = 0, occ_split_bulk = 0;  // resident CTAs per SM of the three scatter kernels
+    int occ_sliced_a = 0, occ_sliced_b = 0;
     int hist_occ = 0;
     bool rank_atoms = false;  // rank keys with returning shared atomics (self-tested) instead of ballots
 };
@@ -189,7 +196,8 @@ static cudaError_t dev_info(DevInfo **out)
             {(const void *)KERNEL_SPLIT_BULK(7), (int)sizeof(SmemSplitBulk)}, {(const void *)KERNEL_SPLIT_BULK(15), (int)sizeof(SmemSplitBulk)},
             {(const void *)KERNEL_B(8), (int)sizeof(SmemB)},     {(const void *)KERNEL_B(0), (int)sizeof(SmemB)},
             {(const void *)KERNEL_SPLIT(1), (int)sizeof(SmemSplit)},  {(const void *)KERNEL_SPLIT(3), (int)sizeof(SmemSplit)},
-            {(const void *)KERNEL_SPLIT(7), (int)sizeof(SmemSplit)},  {(const void *)KERNEL_SPLIT(15), (int)sizeof(SmemSplit)}};
+            {(const void *)KERNEL_SPLIT(7), (int)sizeof(SmemSplit)},  {(const void *)KERNEL_SPLIT(15), (int)sizeof(SmemSplit)},
+            {(const void *)KERNEL_SLICED_A, (int)sizeof(SmemSlicedA)}, {(const void *)KERNEL_SLICED_B, (int)sizeof(SmemSlicedB)}};
         for (auto &k : kernels) {
             e = cudaFuncSetAttribute(k.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, k.smem);
             if (e != cudaSuccess) return e;
@@ -203,6 +211,10 @@ static cudaError_t dev_info(DevInfo **out)
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.occ_b, KERNEL_B(8), SORT_THREADS, sizeof(SmemB));
         if (e != cudaSuccess) return e;
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.occ_split, KERNEL_SPLIT(15), SORT_THREADS, sizeof(SmemSplit));
+        if (e != cudaSuccess) return e;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.occ_sliced_a, KERNEL_SLICED_A, SORT_THREADS, sizeof(SmemSlicedA));
+        if (e != cudaSuccess) return e;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.occ_sliced_b, KERNEL_SLICED_B, SORT_THREADS, sizeof(SmemSlicedB));
         if (e != cudaSuccess) return e;
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.hist_occ, k_histogram<4, HIST_THREADS, HIST_REPL>,
                                                           HIST_THREADS, 0);
@@ -485,6 +497,78 @@ cudaError_t scatter_by_splitters(const uint32_t *in, size_t n, const uint32_t *s
         auto kern = nsplit <= 1 ? KERNEL_SPLIT(1) : nsplit <= 3 ? KERNEL_SPLIT(3) : nsplit <= 7 ? KERNEL_SPLIT(7) : KERNEL_SPLIT(15);
         kern<<<grid, SORT_THREADS, sizeof(SmemSplit), st>>>(in, nullptr, (uint32_t)n, arg, d_ptrs, nullptr, ws + WS_DESC,
                                                             ws + WS_TICKET, (uint32_t)ntiles, use_tma);
+    }
+    return cudaGetLastError();
+}
+
+// ---- step-wise distributed LSD sort (one global counting sort per digit) -----------
+size_t step_table_bytes() { return sizeof(SliceTable); }
+
+cudaError_t step_table_init(void *d_table, const unsigned long long *peers, const unsigned long long *slice_starts,
+                            int nslice, cudaStream_t st)
+{
+    if (nslice < 1 || nslice > MAX_SLICES || !d_table) return cudaErrorInvalidValue;
+    DevInfo *dev = nullptr;
+    CK(dev_info(&dev));
+    const size_t tile = dev->rank_atoms ? kTileA : kTileB;
+    SliceTable h{};
+    for (int j = 0; j < nslice; j++) {
+        // a bucket's run inside one tile may cross at most one slice boundary
+        if (slice_starts[j + 1] < slice_starts[j] || slice_starts[j + 1] > 0xffffffffull) return cudaErrorInvalidValue;
+        if (j + 1 < nslice && slice_starts[j + 1] - slice_starts[j] < tile) return cudaErrorInvalidValue;
+        h.peer[j] = peers[j];
+        h.slice_start[j] = (uint32_t)slice_starts[j];
+    }
+    for (int j = nslice; j <= MAX_SLICES; j++) h.slice_start[j] = (uint32_t)slice_starts[nslice];
+    h.nslice = (uint32_t)nslice;
+    // everything up to gbase (that part is written by step_bases); pageable source: staged before return
+    return cudaMemcpyAsync(d_table, &h, offsetof(SliceTable, gbase), cudaMemcpyHostToDevice, st);
+}
+
+cudaError_t step_counts(const uint32_t *in, size_t n, uint32_t shift, uint32_t nbits, uint32_t *d_counts, cudaStream_t st)
+{
+    if (nbits < 1 || nbits > 8 || shift + nbits > 32 || n > 0xffffffffull) return cudaErrorInvalidValue;
+    DevInfo *dev = nullptr;
+    CK(dev_info(&dev));
+    CK(cudaMemsetAsync(d_counts, 0, RADIX * sizeof(uint32_t), st));
+    if (n == 0) return cudaSuccess;
+    PassPlan plan{};
+    plan.npass = 1;
+    plan.shift[0] = shift;
+    plan.mask[0] = (1u << nbits) - 1;
+    CK(launch_hist<1>(in, n, plan, d_counts, dev->sms, dev->hist_occ, st));
+    return cudaGetLastError();
+}
+
+cudaError_t step_bases(const uint32_t *d_gathered, int nranks, int me, void *d_table, cudaStream_t st)
+{
+    if (nranks < 1 || nranks > MAX_SLICES || me < 0 || me >= nranks) return cudaErrorInvalidValue;
+    k_step_bases<<<1, RADIX, 0, st>>>(d_gathered, nranks, me, static_cast<SliceTable *>(d_table));
+    return cudaGetLastError();
+}
+
+cudaError_t step_scatter(const uint32_t *in, size_t n, uint32_t shift, uint32_t nbits, const void *d_table,
+                         void *workspace, size_t workspace_len, cudaStream_t st)
+{
+    if (nbits < 1 || nbits > 8 || shift + nbits > 32 || n >= (1ull << 30)) return cudaErrorInvalidValue;
+    if (n == 0) return cudaSuccess;
+    if (workspace_len < workspace_bytes(n) || !workspace || !d_table) return cudaErrorInvalidValue;
+    DevInfo *dev = nullptr;
+    CK(dev_info(&dev));
+    uint32_t *ws = static_cast<uint32_t *>(workspace);
+    const int tile = dev->rank_atoms ? kTileA : kTileB;
+    const size_t ntiles = num_tiles(n, tile);
+    CK(cudaMemsetAsync(ws + WS_TICKET, 0, (WS_DESC - WS_TICKET + ntiles * RADIX) * sizeof(uint32_t), st));
+    const RadixBinner::Arg arg{shift, (1u << nbits) - 1};
+    const int use_tma = (reinterpret_cast<uintptr_t>(in) & 15u) == 0;
+    if (dev->rank_atoms) {
+        const int grid = (int)std::min<size_t>(ntiles, (size_t)dev->sms * dev->occ_sliced_a);
+        KERNEL_SLICED_A<<<grid, SORT_THREADS, sizeof(SmemSlicedA), st>>>(in, nullptr, (uint32_t)n, arg, d_table, nullptr,
+                                                                         ws + WS_DESC, ws + WS_TICKET, (uint32_t)ntiles, use_tma);
+    } else {
+        const int grid = (int)std::min<size_t>(ntiles, (size_t)dev->sms * dev->occ_sliced_b);
+        KERNEL_SLICED_B<<<grid, SORT_THREADS, sizeof(SmemSlicedB), st>>>(in, nullptr, (uint32_t)n, arg, d_table, nullptr,
+                                                                         ws + WS_DESC, ws + WS_TICKET, (uint32_t)ntiles, use_tma);
     }
     return cudaGetLastError();
 }

@@ -58,6 +58,26 @@ cudaError_t scatter_by_splitters(const uint32_t *in, size_t n, const uint32_t *s
                                  const unsigned long long *dest_ptrs, void *workspace, size_t workspace_len,
                                  cudaStream_t st);
 
+// Step-wise distributed LSD sort: the reference's P-worker protocol -- every
+// step, each worker sorts its slice by one digit and the slices are regathered bucket-major,
+// worker-minor (localTest/benchmarks.cpp:70-160, benchmark/pkg/sort/distrib.go:119-175) -- is one
+// GLOBAL stable counting sort per digit.  Here the scatter pass of rank `me` writes each key
+// straight to its global position, i.e. into the slice of the GPU that owns that position:
+//   step_counts : digit histogram of the local slice (256 words)
+//   (all-gather of the P x 256 counts: the caller's collective)
+//   step_bases  : global position of this rank's first key of every digit -> table
+//   step_scatter: the scatter pass with sliced output (peer stores over NVLink)
+// The table (step_table_bytes() of device memory) maps positions to slices: slice j holds global
+// positions [slice_starts[j], slice_starts[j+1]) at device address peers[j]; every slice but the
+// last must be at least one scatter tile long.  n < 2^30 per rank, total < 2^32.
+size_t step_table_bytes();
+cudaError_t step_table_init(void *d_table, const unsigned long long *peers, const unsigned long long *slice_starts,
+                            int nslice, cudaStream_t st);
+cudaError_t step_counts(const uint32_t *in, size_t n, uint32_t shift, uint32_t nbits, uint32_t *d_counts, cudaStream_t st);
+cudaError_t step_bases(const uint32_t *d_gathered, int nranks, int me, void *d_table, cudaStream_t st);
+cudaError_t step_scatter(const uint32_t *in, size_t n, uint32_t shift, uint32_t nbits, const void *d_table,
+                         void *workspace, size_t workspace_len, cudaStream_t st);
+
 // Test hook: cap the number of tiles per look-back portion (0 = default,
 // i.e. the largest portion whose key count fits the 30-bit descriptors).
 void debug_set_portion_tiles(uint32_t tiles);

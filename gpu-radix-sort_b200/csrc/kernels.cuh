@@ -384,7 +384,21 @@ __device__ __noinline__ void rank_tile_heavy(const uint32_t *keys, Smem *sp)
     }
 }
 
-template <int THREADS, int KPT, bool PTR_OUT, class BinnerArg>
+// Where a scatter pass writes: OUT_INDEX -- bucket bases are indices into `out`; OUT_PTR -- one
+// 64-bit destination address per bin (local or NVLink-mapped peer memory; the splitter exchange);
+// OUT_SLICED -- bucket bases are positions in ONE array that is cut into contiguous slices living
+// on different GPUs (the step-wise distributed LSD sort): a SliceTable maps a position to its owner.
+constexpr int OUT_INDEX = 0, OUT_PTR = 1, OUT_SLICED = 2;
+constexpr int MAX_SLICES = 16;
+struct SliceTable {                        // device memory, one per rank
+    unsigned long long peer[MAX_SLICES];   // where slice j lives (its first key), as seen from this GPU
+    uint32_t slice_start[MAX_SLICES + 1];  // global position of slice j's first key; [nslice] = total keys
+    uint32_t nslice;
+    uint32_t pad_[2];
+    uint32_t gbase[RADIX];                 // global position of this rank's first key of every digit (k_step_bases)
+};
+
+template <int THREADS, int KPT, int PTR_OUT, class BinnerArg>
 struct OnesweepSmem {
     static constexpr int KEYS_PER_THREAD = KPT;
     static constexpr int TILE = THREADS * KPT;
@@ -393,13 +407,20 @@ struct OnesweepSmem {
     uint32_t warp_hist[NWARPS][RADIX];         // per-warp digit counters -> running BYTE offsets into keys[]
     // global destination of bucket b minus its start in the tile: an index into `out`,
     // or (PTR_OUT) a byte address, possibly in peer memory
-    typename std::conditional<PTR_OUT, unsigned long long, uint32_t>::type tile_dst[RADIX];
+    typename std::conditional<PTR_OUT != OUT_INDEX, unsigned long long, uint32_t>::type tile_dst[RADIX];
     uint32_t s_warp[8];
     alignas(8) uint64_t mbar;
     uint32_t next_tile;
     BinnerArg binner_arg;  // copy for the out-of-line heavy-tile path
     uint32_t heavy_d4;  // 4 * (a digit holding more than a quarter of the current tile), valid when the tile votes heavy
-    uint32_t bucket_start[PTR_OUT ? MAX_SPLITTERS + 2 : 1];  // position-binned write-out (SplitBinner): bucket b starts here
+    uint32_t bucket_start[PTR_OUT == OUT_PTR ? MAX_SPLITTERS + 2 : 1];  // position-binned write-out (SplitBinner): bucket b starts here
+    // OUT_SLICED: a bucket's run in this tile may straddle one slice boundary -- keys at tile positions
+    // >= split[b] use tile_dst_hi[b] (the next slice's owner) instead of tile_dst[b]
+    unsigned long long tile_dst_hi[PTR_OUT == OUT_SLICED ? RADIX : 1];
+    uint32_t split[PTR_OUT == OUT_SLICED ? RADIX : 1];
+    unsigned long long peer[PTR_OUT == OUT_SLICED ? MAX_SLICES : 1];
+    uint32_t slice_start[PTR_OUT == OUT_SLICED ? MAX_SLICES + 1 : 1];
+    uint32_t nslice;
 };
 
 constexpr int RANK_BALLOT = 0;  // one vote.ballot per digit bit + a leader atomic: architecturally ordered
@@ -409,14 +430,15 @@ constexpr int RANK_ATOMS = 1;   // rank = return value of the warp's shared atom
 // descriptor value).  base: global bucket bases for this portion;
 // base_next (nullable): receives base + portion bucket totals for the next
 // portion.  desc: ntiles x 256 zero-initialised descriptors; ticket: zeroed.
-// PTR_OUT: `base` holds one 64-bit destination pointer per bin (local or
-// NVLink-mapped peer memory) instead of an offset into `out`.
+// PTR_OUT (an OUT_* mode): OUT_PTR -- `base` holds one 64-bit destination pointer per
+// bin (local or NVLink-mapped peer memory) instead of an offset into `out`;
+// OUT_SLICED -- `base` is a SliceTable (slices >= one tile long, single portion).
 //
 // One tile per loop trip, one 1-D bulk TMA per tile.  The ticket for a tile is
 // taken only when the CTA is about to load it, so tiles publish their counts
 // in (nearly) ticket order and a look-back rarely meets an unpublished
 // predecessor; load latency is covered by the other CTAs resident on the SM.
-template <int THREADS, int KPT, int MINB, int RANK, int NBITS, int LB, class Binner, bool PTR_OUT>
+template <int THREADS, int KPT, int MINB, int RANK, int NBITS, int LB, class Binner, int PTR_OUT>
 __global__ void __launch_bounds__(THREADS, MINB)
     k_onesweep(const uint32_t *__restrict__ in, uint32_t *__restrict__ out, uint32_t n, const typename Binner::Arg binner_arg,
                const void *__restrict__ base_v, uint32_t *__restrict__ base_next, uint32_t *__restrict__ desc,
@@ -430,7 +452,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Smem &s = *reinterpret_cast<Smem *>(smem_raw);
 
-    if (!PTR_OUT && ticket[SKIP_OFFSET]) {  // constant digit (k_scan_hist): the pass is a copy
+    if (PTR_OUT == OUT_INDEX && ticket[SKIP_OFFSET]) {  // constant digit (k_scan_hist): the pass is a copy
         copy_keys(in, out, n);
         return;
     }
@@ -461,6 +483,12 @@ __global__ void __launch_bounds__(THREADS, MINB)
         s.next_tile = t;
         s.binner_arg = binner_arg;
         if (use_tma && t < ntiles) issue_load(t);
+    }
+    if (PTR_OUT == OUT_SLICED) {  // the slice map, once per CTA
+        const SliceTable *tab = static_cast<const SliceTable *>(base_v);
+        if (tid < MAX_SLICES) s.peer[tid] = tab->peer[tid];
+        if (tid <= MAX_SLICES) s.slice_start[tid] = tab->slice_start[tid];
+        if (tid == 0) s.nslice = tab->nslice;
     }
 #pragma unroll
     for (int j = lane; j < RADIX; j += 32) s.warp_hist[warp][j] = 0;
@@ -597,8 +625,18 @@ __global__ void __launch_bounds__(THREADS, MINB)
                 st_relaxed(&desc[(size_t)cur * RADIX + tid], DESC_INCL | (excl + my_count));
             }
             const uint32_t my_start = my_start4 >> 2;
-            if (PTR_OUT && Binner::kByPosition && tid <= MAX_SPLITTERS + 1) s.bucket_start[tid] = my_start;
-            if (PTR_OUT) {
+            if (PTR_OUT == OUT_PTR && Binner::kByPosition && tid <= MAX_SPLITTERS + 1) s.bucket_start[tid] = my_start;
+            if (PTR_OUT == OUT_SLICED) {
+                // this tile's run of bucket `tid` starts at global position g: find the slice it falls
+                // into; the part of the run past that slice's end goes to the next slice's owner
+                const uint32_t g = static_cast<const SliceTable *>(base_v)->gbase[tid] + excl;
+                uint32_t j = 0;
+                for (uint32_t k = 1; k < s.nslice; k++) j += g >= s.slice_start[k] ? 1u : 0u;
+                const uint32_t sp = my_start + (s.slice_start[j + 1] - g);  // tile position where slice j+1 begins
+                s.tile_dst[tid] = s.peer[j] + 4ull * (unsigned long long)(g - s.slice_start[j]) - 4ull * (unsigned long long)my_start;
+                s.tile_dst_hi[tid] = (j + 1 < s.nslice ? s.peer[j + 1] : 0ull) - 4ull * (unsigned long long)sp;
+                s.split[tid] = sp;
+            } else if (PTR_OUT == OUT_PTR) {
                 const unsigned long long gptr = static_cast<const unsigned long long *>(base_v)[tid];
                 s.tile_dst[tid] = gptr + 4ull * (unsigned long long)excl - 4ull * (unsigned long long)my_start;
             } else {
@@ -630,7 +668,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
         for (int i = 0; i < KPT; i++) {
             const uint32_t p = tid + i * THREADS;
             uint32_t d4;
-            if (PTR_OUT && Binner::kByPosition) {
+            if (PTR_OUT == OUT_PTR && Binner::kByPosition) {
                 // equal keys may sit in different buckets: the bucket follows from the position
                 uint32_t d = 0;
                 for (uint32_t b = 1; b <= pad_bin; b++) d += s.bucket_start[b] <= p ? 1u : 0u;
@@ -639,7 +677,12 @@ __global__ void __launch_bounds__(THREADS, MINB)
                 d4 = binner.bin4(key[i]);
             }
             if (valid == TILE || p < valid) {
-                if (PTR_OUT)
+                if (PTR_OUT == OUT_SLICED) {
+                    const uint32_t sp = *reinterpret_cast<const uint32_t *>(reinterpret_cast<const unsigned char *>(s.split) + d4);
+                    const unsigned char *tab = p < sp ? reinterpret_cast<const unsigned char *>(s.tile_dst)
+                                                      : reinterpret_cast<const unsigned char *>(s.tile_dst_hi);
+                    *reinterpret_cast<uint32_t *>(*reinterpret_cast<const unsigned long long *>(tab + 2 * d4) + 4ull * p) = key[i];
+                } else if (PTR_OUT == OUT_PTR)
                     *reinterpret_cast<uint32_t *>(*reinterpret_cast<const unsigned long long *>(
                                                       reinterpret_cast<const unsigned char *>(s.tile_dst) + 2 * d4) +
                                                   4ull * p) = key[i];
@@ -768,6 +811,24 @@ __global__ void k_pick_splitters(const uint32_t *__restrict__ sorted, uint32_t n
     const uint32_t r1 = lo;
     if (r1 - r0 >= TIE_MIN_RUN && q > r0 && v != 0xffffffffu)  // 0xffffffff pads partial tiles: never split
         splitters[SPLIT_TIE_OFFSET + g - 1] = (uint32_t)((((unsigned long long)(q - r0)) << 32) / (r1 - r0));
+}
+
+// Step-wise distributed LSD sort: gathered[k][d] = keys of digit d on rank k.  The global array
+// after the step is bucket-major, rank-minor (the reference's regather order, localTest/
+// benchmarks.cpp:120-136, benchmark/pkg/sort/helpers.go:67-78), so rank `me`'s first key of digit
+// d lands at  sum over digits < d of all ranks' counts  +  sum over ranks < me of their digit-d counts.
+__global__ void __launch_bounds__(RADIX) k_step_bases(const uint32_t *__restrict__ gathered, int nranks, int me,
+                                                      SliceTable *__restrict__ tab)
+{
+    __shared__ uint32_t s_warp[8];
+    const int d = threadIdx.x;
+    uint32_t tot = 0, before = 0;
+    for (int k = 0; k < nranks; k++) {
+        const uint32_t c = gathered[k * RADIX + d];
+        tot += c;
+        if (k < me) before += c;
+    }
+    tab->gbase[d] = block_excl_scan_256(tot, s_warp, nullptr) + before;
 }
 
 __global__ void k_store_ptrs(const PtrTable t, unsigned long long *__restrict__ dst)

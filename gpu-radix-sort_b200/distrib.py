@@ -15,6 +15,12 @@ single exchange:
        nccl: partition locally with the same kernel, then NCCL all_to_all_single
   4. local LSD sort of what arrived (libsortDeviceSort, 4 passes)
 
+sort_stepwise() is the reference's OWN distributed algorithm on the same plumbing (SURVEY.md 8(f)
+N2): one global counting sort per 8-bit digit, 32/8 exchanges, every key stored straight into the
+slice of the GPU that owns its global position.  Same intermediate states as the reference after
+every step, perfectly balanced output (slices keep their sizes) for any input, no sampling -- but
+four trips over NVLink instead of one.
+
 Rank r ends up with the r-th value range, ascending.  torch.distributed is the
 plumbing (collectives, rendezvous); all key movement and sorting on the GPU is
 libsort.so.  A key value heavy enough to span a splitter has its copies cut
@@ -121,12 +127,19 @@ class DistributedSorter:
         self.token = torch.zeros(1, dtype=i32, device=dev)
         self.h_counts = torch.empty(16 * self.world, dtype=i32).pin_memory()
         self.seed = 1
+        self._step = None      # lazily built state of sort_stepwise()
         # kernels per sort: sample, sample sort (hist, scan, 4 passes), pick, dest hist, store ptrs,
         # scatter, local sort (hist, scan, 4 passes)
         self.launches_per_sort = 1 + 6 + 1 + 1 + 1 + 1 + 6
+        self.launches_per_stepwise_sort = 4 * 3    # per step: histogram, bases, scatter
         self.last_totals = None
 
     def close(self):
+        if self._step is not None:
+            for p in self._step["opened"]:
+                self.lib.libsortIpcClose(p)
+            self.lib.libsortIpcFree(self._step["recv2_ptr"])
+            self._step = None
         for p in self._opened:
             self.lib.libsortIpcClose(p)
         self._opened = []
@@ -210,6 +223,98 @@ class DistributedSorter:
         if ev:
             ev("local_sort")
         return self.out[:nrecv], nrecv
+
+    # ------------------------------------------------------------- step-wise --
+    def _map_on_peers(self, ptr):
+        """cudaIpc-export a local allocation and open everybody else's: [address of rank r's buffer as seen here]."""
+        L, W = self.lib, self.world
+        ptrs, opened = [ptr] * W, []
+        if W > 1:
+            handle = (ctypes.c_uint8 * 64)()
+            binding.check(L.libsortIpcExport(ptr, handle), "libsortIpcExport")
+            mine = torch.tensor(list(handle), dtype=torch.uint8, device=self.dev)
+            allh = torch.empty(W * 64, dtype=torch.uint8, device=self.dev)
+            dist.all_gather_into_tensor(allh, mine, group=self.group)
+            allh = allh.cpu().numpy().reshape(W, 64)
+            for r in range(W):
+                if r != self.rank:
+                    q = ctypes.c_void_p()
+                    binding.check(L.libsortIpcOpen((ctypes.c_uint8 * 64)(*allh[r].tolist()), ctypes.byref(q)),
+                                  "libsortIpcOpen(rank %d)" % r)
+                    ptrs[r] = q.value
+                    opened.append(q.value)
+        return ptrs, opened
+
+    def _enable_stepwise(self):
+        if self._step is not None:
+            return self._step
+        if self.mode != "p2p":
+            raise ValueError("sort_stepwise needs the p2p exchange (peer-mapped slices)")
+        L, dev, i32, W = self.lib, self.dev, torch.int32, self.world
+        p = ctypes.c_void_p()
+        binding.check(L.libsortIpcAlloc(self.cap * 4, ctypes.byref(p)), "libsortIpcAlloc")
+        peers2, opened = self._map_on_peers(p.value)
+        tb = L.libsortStepTableBytes()
+        self._step = {
+            "recv2_ptr": p.value, "recv2": _as_tensor(p.value, self.cap, dev), "opened": opened,
+            "peers": [self.peer_ptrs, peers2],              # ping-pong: slices live in recv, then in recv2, ...
+            "tables": [torch.zeros(tb, dtype=torch.uint8, device=dev) for _ in range(2)],
+            "counts": torch.zeros(256, dtype=i32, device=dev), "gathered": torch.zeros(256 * W, dtype=i32, device=dev),
+            "lens": torch.zeros(W, dtype=torch.int64, device=dev), "layout": None,
+        }
+        return self._step
+
+    def sort_stepwise(self, keys, ev=None, on_step=None):
+        """The reference's step-wise distributed LSD sort (8-bit steps) with device-resident slices.
+        Rank r keeps exactly keys.numel() keys: afterwards they are the r-th slice of the sorted whole.
+        Returns (tensor view of the slice, its length); valid until the next sort on this object.
+        on_step(k, view) is called after step k with this rank's slice of the intermediate array."""
+        if keys.dtype not in (torch.int32, torch.uint32) or not keys.is_cuda or not keys.is_contiguous():
+            raise ValueError("keys must be a contiguous CUDA int32/uint32 tensor")
+        L, st, n, W, me = self.lib, self._stream(), keys.numel(), self.world, self.rank
+        if n > self.cap:
+            raise ValueError("slice larger than the sorter was built for")
+        S = self._enable_stepwise()
+        if W > 1:
+            dist.all_gather_into_tensor(S["lens"], torch.tensor([n], dtype=torch.int64, device=self.dev), group=self.group)
+            lens = S["lens"].cpu().tolist()
+        else:
+            lens = [n]
+        if S["layout"] != lens:
+            starts = [0]
+            for x in lens:
+                starts.append(starts[-1] + x)
+            arr_s = (ctypes.c_uint64 * (W + 1))(*starts)
+            for k in range(2):
+                arr_p = (ctypes.c_uint64 * W)(*S["peers"][k])
+                binding.check(L.libsortStepTableInit(S["tables"][k].data_ptr(), arr_p, arr_s, W, st),
+                              "slice table (every slice but the last needs >= %d keys)" % L.libsortTileKeys())
+            S["layout"] = lens
+        src, bufs = keys.data_ptr(), [self.recv, S["recv2"]]
+        shift = k = 0
+        while shift < 32:
+            nb = min(8, 32 - shift)
+            table = S["tables"][k & 1]
+            binding.check(L.libsortStepCounts(src, n, shift, nb, S["counts"].data_ptr(), st), "step counts")
+            if W > 1:
+                dist.all_gather_into_tensor(S["gathered"], S["counts"], group=self.group)
+            else:
+                S["gathered"].copy_(S["counts"])
+            binding.check(L.libsortStepBases(S["gathered"].data_ptr(), W, me, table.data_ptr(), st), "step bases")
+            binding.check(L.libsortStepScatter(src, n, shift, nb, table.data_ptr(), self.ws.data_ptr(), self.ws.numel(), st),
+                          "step scatter")
+            if W > 1:
+                # every rank's stores of this step have landed, and nobody still reads the buffer the
+                # next step overwrites
+                dist.all_reduce(self.token, group=self.group)
+            out = bufs[k & 1]
+            src, shift, k = out.data_ptr(), shift + nb, k + 1
+            if ev:
+                ev("step%d" % k)
+            if on_step:
+                on_step(k, out[:n])
+        self.last_totals = np.asarray(lens)
+        return out[:n], n
 
     # ---------------------------------------------------------- verification --
     def verify(self, keys, out, nrecv):

@@ -109,6 +109,33 @@ LIBSORT_API int libsortIpcClose(void *ptr);
  */
 LIBSORT_API int libsortDistribSort(uint32_t *h_keys, size_t n, int ngpu);
 
+/*
+ * Step-wise distributed LSD sort on device buffers: the reference's own distributed
+ * algorithm (P workers; every step each worker sorts its slice by one digit, then the
+ * slices are regathered bucket-major / worker-minor: localTest/benchmarks.cpp:70-160,
+ * benchmark/pkg/sort/distrib.go:119-175, helpers.go:67-78) with the host shuffle replaced
+ * by peer stores.  A step is one GLOBAL stable counting sort by the digit:
+ *   libsortStepCounts   digit histogram of this rank's slice -> d_counts[256]
+ *   (all-gather the P x 256 counts with the caller's collective)
+ *   libsortStepBases    d_gathered[P][256] -> where this rank's first key of every digit goes
+ *   libsortStepScatter  the scatter pass; each key is stored at its global position, i.e. into
+ *                       the slice of whichever GPU owns that position (local or NVLink-mapped)
+ * The slice table (libsortStepTableBytes() of device memory, filled by libsortStepTableInit
+ * from HOST arrays) says where slice j lives (peers[j]) and which global positions it holds
+ * ([slice_starts[j], slice_starts[j+1])); every slice but the last must be at least
+ * libsortTileKeys() long, n < 2^30 per rank, total < 2^32.  Intermediate states equal the
+ * reference's after every step; after the last step slice r holds the r-th part of the sorted
+ * whole.  See gpu-radix-sort_b200/distrib.py (DistributedSorter.sort_stepwise).
+ */
+LIBSORT_API size_t libsortStepTableBytes(void);
+LIBSORT_API int libsortStepTableInit(void *d_table, const unsigned long long *peers,
+                                     const unsigned long long *slice_starts, int nslice, void *stream);
+LIBSORT_API int libsortStepCounts(const uint32_t *d_in, size_t n, uint32_t shift, uint32_t nbits, uint32_t *d_counts,
+                                  void *stream);
+LIBSORT_API int libsortStepBases(const uint32_t *d_gathered, int nranks, int me, void *d_table, void *stream);
+LIBSORT_API int libsortStepScatter(const uint32_t *d_in, size_t n, uint32_t shift, uint32_t nbits, const void *d_table,
+                                   void *d_workspace, size_t workspace_bytes, void *stream);
+
 /* populateInput at an explicit stream position: arr[i] = element first+i of the
  * fresh-process PCG sequence (reference libsort/utils.cu:63-79).  Thread safe. */
 LIBSORT_API void libsortPopulateInputAt(uint32_t *arr, size_t nelem, uint64_t first);

@@ -85,6 +85,24 @@ def main():
                     assert stats["imbalance"] < 1.1, (kind, stats)
                 if rank == 0:
                     print(exch, kind, "ok; keys/rank", stats["keys_per_rank"], "imbalance %.3f" % stats["imbalance"])
+            if exch == "p2p":
+                # the reference's step-wise protocol: intermediate state after step k == the whole array
+                # stably sorted by its low 8k bits, cut back into the ranks' slices
+                for kind in ("uniform", "zipf", "allequal"):
+                    keys = shard(rank, n, kind)
+                    d = torch.from_numpy(keys.view(np.int32)).cuda()
+                    allkeys = np.concatenate([shard(r, n, kind) for r in range(world)])
+                    seen = []
+                    out, cnt = sorter.sort_stepwise(d, on_step=lambda k, v: seen.append(v.cpu().numpy().view(np.uint32).copy()))
+                    assert cnt == n and len(seen) == 4
+                    state = allkeys
+                    for k in range(4):
+                        state = state[np.argsort((state >> np.uint32(8 * k)) & np.uint32(0xFF), kind="stable")]
+                        assert np.array_equal(seen[k], state[rank * n:(rank + 1) * n]), (kind, "step", k + 1)
+                    assert np.array_equal(out.cpu().numpy().view(np.uint32), np.sort(allkeys)[rank * n:(rank + 1) * n]), kind
+                    sorter.verify(d, out, cnt)
+                    if rank == 0:
+                        print("stepwise", kind, "ok")
             sorter.close()
     dist.barrier()
     dist.destroy_process_group()

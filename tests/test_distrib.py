@@ -64,3 +64,4 @@ def test_distributed_sort_on_gpus():
     r = torchrun(world, 29741, "nccl", 300000, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
     assert r.stdout.count(" ok; keys/rank") == 10
+    assert r.stdout.count("stepwise") == 3

@@ -269,3 +269,47 @@ def test_distrib_sort_host_call(gpu_lib, oracle, n):
     assert gpu_lib.libsortDistribSort(got.ctypes.data, n, 0) == 1
     assert np.array_equal(got, want)
     assert gpu_lib.libsortDistribSort(got.ctypes.data, n, 99) == 0      # more GPUs than any pool has
+
+
+@pytest.mark.parametrize("lens", [[40000], [30000, 30000], [20000, 31111, 15000, 7], [14336, 14336, 14336, 14336, 1]])
+def test_stepwise_blocks_virtual_ranks(gpu_lib, oracle, pkg, lens):
+    """The step-wise distributed LSD building blocks (libsortStep*) with several VIRTUAL ranks on one GPU:
+    each rank's scatter stores every key at its global position inside whichever slice owns it.  After step
+    k the whole array must be the input stably sorted by its low 8k bits -- the reference distribSort's
+    intermediate state (localTest/benchmarks.cpp:70-160) -- for uniform and skewed keys."""
+    import ctypes
+    import torch
+    L, P, total = gpu_lib, len(lens), sum(lens)
+    starts = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    st = torch.cuda.current_stream().cuda_stream
+    x = oracle.pcg_stream(total)
+    cases = {"uniform": x, "lowbyte": (x & np.uint32(0xFF0000FF)).astype(np.uint32), "equal": np.full(total, 0xA5A5A5A5, np.uint32)}
+    tb = L.libsortStepTableBytes()
+    ws = torch.empty(L.libsortWorkspaceBytes(max(lens)), dtype=torch.uint8, device="cuda")
+    for name, keys in cases.items():
+        bufs = [torch.from_numpy(keys.view(np.int32)).cuda(), torch.empty(total, dtype=torch.int32, device="cuda")]
+        tables = [torch.zeros(tb, dtype=torch.uint8, device="cuda") for _ in range(2)]
+        for k in range(2):
+            peers = (ctypes.c_uint64 * P)(*[bufs[k].data_ptr() + 4 * int(starts[r]) for r in range(P)])
+            pkg.binding.check(L.libsortStepTableInit(tables[k].data_ptr(), peers, (ctypes.c_uint64 * (P + 1))(*starts.tolist()), P, st),
+                              "table")
+        gathered = torch.zeros(P * 256, dtype=torch.int32, device="cuda")
+        state = keys
+        for step in range(4):
+            src, dst = bufs[step & 1], (step + 1) & 1
+            for r in range(P):
+                pkg.binding.check(L.libsortStepCounts(src.data_ptr() + 4 * int(starts[r]), lens[r], 8 * step, 8,
+                                                      gathered.data_ptr() + 1024 * r, st), "counts")
+            for r in range(P):      # every virtual rank: bases, then its scatter into the other buffer's slices
+                pkg.binding.check(L.libsortStepBases(gathered.data_ptr(), P, r, tables[dst].data_ptr(), st), "bases")
+                pkg.binding.check(L.libsortStepScatter(src.data_ptr() + 4 * int(starts[r]), lens[r], 8 * step, 8,
+                                                       tables[dst].data_ptr(), ws.data_ptr(), ws.numel(), st), "scatter")
+            state = state[np.argsort((state >> np.uint32(8 * step)) & np.uint32(0xFF), kind="stable")]
+            got = bufs[dst].cpu().numpy().view(np.uint32)
+            assert np.array_equal(got, state), (name, lens, "step", step + 1)
+        assert np.array_equal(got, np.sort(keys))
+    # a middle slice shorter than one tile cannot be addressed: rejected, not mis-sorted
+    if P >= 3:
+        bad = np.array([0, 20000, 20010, 60000], dtype=np.int64)
+        peers = (ctypes.c_uint64 * 3)(*[bufs[0].data_ptr()] * 3)
+        assert L.libsortStepTableInit(tables[0].data_ptr(), peers, (ctypes.c_uint64 * 4)(*bad.tolist()), 3, st) != 0
