@@ -272,6 +272,7 @@ struct RadixBinner {
     __device__ __forceinline__ uint32_t bin(uint32_t key, uint32_t) const { return bin(key); }
     __device__ __forceinline__ uint32_t bin4(uint32_t key, uint32_t) const { return bin4(key); }
     static constexpr bool kByPosition = false;  // bin is a function of the key alone
+    static constexpr int kBits = 0;             // digit width known at run time only
     __device__ __forceinline__ uint32_t pad_bin() const { return mask; }  // bin of the 0xffffffff padding keys
     __device__ __forceinline__ int nbits() const { return __popc(mask); }
 };
@@ -336,19 +337,30 @@ struct SplitBinner {
         return min(d, (uint32_t)nsplit);
     }
     __device__ __forceinline__ uint32_t bin4(uint32_t key) const { return bin(key) << 2; }
-    // destination of the key at position idx of the shard: as bin(key), minus the equal splitters
-    // whose threshold the position's hash stays below (uniform branch: most inputs have no ties)
+    // destination of the key at position idx of the shard.  The splitters equal to the key are
+    // [lo, d) with lo = number of splitters < key; the key passes those whose threshold the
+    // position's hash reaches (thresholds ascend inside a run, zeros first).  Uniform test: most
+    // inputs have no ties; divergent branch: only keys that equal a splitter.  (A splitter of
+    // 0xffffffff never has a threshold, so the padding keys stay in the last bin.)
     __device__ __forceinline__ uint32_t bin(uint32_t key, uint32_t idx) const
     {
         uint32_t d = bin(key);
-        if (ties) {  // (a splitter of 0xffffffff never has a threshold, so the padding keys stay in the last bin)
-            const uint32_t h = tie_hash(idx);
-            while (d > 0 && __ldg(table + d - 1) == key && h < __ldg(table + SPLIT_TIE_OFFSET + d - 1)) --d;
+        if (ties && d > 0 && __ldg(table + d - 1) == key) {  // one load tells whether the key equals a splitter at all
+            const uint32_t lo = key ? bin(key - 1u) : 0u;
+            {
+                const uint32_t h = tie_hash(idx);
+                uint32_t c = 0;
+#pragma unroll
+                for (int j = 0; j < NS; j++)  // independent, warp-uniform loads
+                    c += ((uint32_t)j >= lo && (uint32_t)j < d && h >= __ldg(table + SPLIT_TIE_OFFSET + j)) ? 1u : 0u;
+                d = lo + c;
+            }
         }
         return d;
     }
     __device__ __forceinline__ uint32_t bin4(uint32_t key, uint32_t idx) const { return bin(key, idx) << 2; }
     static constexpr bool kByPosition = true;  // equal keys may sit in different bins
+    static constexpr int kBits = NS == 1 ? 1 : NS == 3 ? 2 : NS == 7 ? 3 : 4;  // bits of a bin index, at compile time
     __device__ __forceinline__ uint32_t pad_bin() const { return (uint32_t)nsplit; }
     __device__ __forceinline__ int nbits() const { return 32 - __clz(nsplit); }  // bins 0..nsplit
 };
@@ -525,10 +537,16 @@ __global__ void __launch_bounds__(THREADS, MINB)
         __syncwarp();  // this warp's counters were zeroed by other lanes
 
         // (2) early counts: per-warp digit histogram (adding 1 lets same-digit lanes be merged)
-#pragma unroll
         //     (indexed with bin(), not bin4(): a different expression than (4) uses, so that the
-        //     optimiser recomputes the address there instead of spilling KPT of them across barriers)
-        for (int i = 0; i < KPT; i++) atomicAdd(&s.warp_hist[warp][binner.bin(key[i], tile_base + wbase + i * 32)], 1u);
+        //     optimiser recomputes the address there instead of spilling KPT of them across barriers).
+        //     A splitter bin costs a binary search and depends on the position: kept, 4 bits per key.
+        uint32_t dig[Binner::kByPosition ? (KPT + 7) / 8 : 1] = {};
+#pragma unroll
+        for (int i = 0; i < KPT; i++) {
+            const uint32_t d = binner.bin(key[i], tile_base + wbase + i * 32);
+            atomicAdd(&s.warp_hist[warp][d], 1u);
+            if (Binner::kByPosition) dig[i >> 3] |= d << (4 * (i & 7));
+        }
         __syncthreads();
 
         // (3) bin threads: reduce over warps, publish the tile aggregate,
@@ -588,8 +606,9 @@ __global__ void __launch_bounds__(THREADS, MINB)
             const uint32_t hist_addr = smem_u32(my_hist);
 #pragma unroll
             for (int i = 0; i < KPT; i++) {
-                const uint32_t d4 = binner.bin4(key[i], tile_base + wbase + i * 32);
-                const uint32_t peers = match_digit<NBITS>(d4 >> 2, nbits);
+                const uint32_t d4 = Binner::kByPosition ? ((dig[i >> 3] >> (4 * (i & 7))) & 15u) << 2
+                                                        : binner.bin4(key[i], tile_base + wbase + i * 32);
+                const uint32_t peers = match_digit<(Binner::kBits ? Binner::kBits : NBITS)>(d4 >> 2, nbits);
                 const uint32_t before = __popc(peers & lt);
                 const int top = 31 - __clz(peers);  // highest peer lane leads; its `before` + 1 is the group size
                 uint32_t off4 = leader_atom_add(hist_addr + d4, (before + 1u) * 4u, lane == top);

@@ -121,9 +121,15 @@ __global__ void __launch_bounds__(THREADS, MINB)
         }
         __syncwarp();  // this warp's counters were zeroed by other lanes
 
-        // (2) early counts: per-warp digit histogram (see k_onesweep for the bin()/bin4() note)
+        // (2) early counts: per-warp digit histogram (see k_onesweep for the bin()/bin4() note).
+        //     A splitter bin costs a binary search (and depends on the position): keep it, 4 bits per key.
+        uint32_t dig[Binner::kByPosition ? (KPT + 7) / 8 : 1] = {};
 #pragma unroll
-        for (int i = 0; i < KPT; i++) atomicAdd(&s.warp_hist[warp][binner.bin(key[i], tile_base + wbase + i * 32)], 1u);
+        for (int i = 0; i < KPT; i++) {
+            const uint32_t d = binner.bin(key[i], tile_base + wbase + i * 32);
+            atomicAdd(&s.warp_hist[warp][d], 1u);
+            if (Binner::kByPosition) dig[i >> 3] |= d << (4 * (i & 7));
+        }
         __syncthreads();
 
         // (3) bin threads: reduce over warps, publish the tile aggregate, finish the
@@ -207,8 +213,9 @@ __global__ void __launch_bounds__(THREADS, MINB)
             const uint32_t hist_addr = smem_u32(my_hist);
 #pragma unroll
             for (int i = 0; i < KPT; i++) {
-                const uint32_t d4 = binner.bin4(key[i], tile_base + wbase + i * 32);
-                const uint32_t peers = match_digit<0>(d4 >> 2, nbits);
+                const uint32_t d4 = Binner::kByPosition ? ((dig[i >> 3] >> (4 * (i & 7))) & 15u) << 2
+                                                        : binner.bin4(key[i], tile_base + wbase + i * 32);
+                const uint32_t peers = match_digit<Binner::kBits>(d4 >> 2, nbits);
                 const uint32_t before = __popc(peers & lt);
                 const int top = 31 - __clz(peers);  // highest peer lane leads; its `before` + 1 is the group size
                 uint32_t off4 = leader_atom_add(hist_addr + d4, (before + 1u) * 4u, lane == top);
