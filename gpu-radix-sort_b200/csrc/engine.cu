@@ -36,6 +36,15 @@ namespace b200sort {
 #ifndef BALLOT_MINB
 #define BALLOT_MINB 4
 #endif
+// The bulk-copy splitter scatter (the NVLink exchange): 24 keys per thread, 4 CTAs per SM.  More CTAs in
+// flight hide the peer-store latency better than longer runs per bulk copy do (exchange at 2 GPUs:
+// 16/24/32/48/56 keys per thread -> 1.03 / 0.88 / 0.94 / 1.06 / 1.08 ms).
+#ifndef SPLIT_KPT
+#define SPLIT_KPT 24
+#endif
+#ifndef SPLIT_BULK_MINB
+#define SPLIT_BULK_MINB 4
+#endif
 #ifndef SPLIT_MINB
 #define SPLIT_MINB 3   // the splitter scatter keeps up to 15 splitters in registers
 #endif
@@ -56,8 +65,9 @@ using SmemSplit = OnesweepSmem<SORT_THREADS, BALLOT_KPT, true, SplitArg>;
 #define KERNEL_A(NBITS) k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, RANK_ATOMS, NBITS, SORT_LB, RadixBinner, false>
 #define KERNEL_BULK k_onesweep_bulk<SORT_THREADS, SORT_KPT, SORT_MINB, SORT_LB, RANK_ATOMS, RadixBinner, false>
 using SmemBulk = BulkSmem<SORT_THREADS, SORT_KPT, RadixBinner::Arg>;
-#define KERNEL_SPLIT_BULK(NS) k_onesweep_bulk<SORT_THREADS, BALLOT_KPT, SPLIT_MINB, SORT_LB, RANK_BALLOT, SplitBinner<NS>, true>
-using SmemSplitBulk = BulkSmem<SORT_THREADS, BALLOT_KPT, SplitArg>;
+#define KERNEL_SPLIT_BULK(NS) k_onesweep_bulk<SORT_THREADS, SPLIT_KPT, SPLIT_BULK_MINB, SORT_LB, RANK_BALLOT, SplitBinner<NS>, true>
+using SmemSplitBulk = BulkSmem<SORT_THREADS, SPLIT_KPT, SplitArg>;
+constexpr int kTileSplitBulk = SORT_THREADS * SPLIT_KPT;
 #define KERNEL_B(NBITS) k_onesweep<SORT_THREADS, BALLOT_KPT, BALLOT_MINB, RANK_BALLOT, NBITS, SORT_LB, RadixBinner, false>
 #define KERNEL_SPLIT(NS) k_onesweep<SORT_THREADS, BALLOT_KPT, SPLIT_MINB, RANK_BALLOT, 0, SORT_LB, SplitBinner<NS>, true>
 // the radix scatter writing into an array sliced over several GPUs (step-wise distributed LSD sort)
@@ -478,7 +488,8 @@ cudaError_t scatter_by_splitters(const uint32_t *in, size_t n, const uint32_t *s
     DevInfo *dev = nullptr;
     CK(dev_info(&dev));
     uint32_t *ws = static_cast<uint32_t *>(workspace);
-    const size_t ntiles = num_tiles(n, kTileB);
+    const bool bulk = g_bulk_exchange && dev->occ_split_bulk > 0;
+    const size_t ntiles = num_tiles(n, bulk ? kTileSplitBulk : kTileB);
     CK(cudaMemsetAsync(ws, 0, (WS_DESC + ntiles * RADIX) * sizeof(uint32_t), st));
     PtrTable t{};
     for (int i = 0; i <= nsplit; i++) t.p[i] = dest_ptrs[i];
@@ -487,7 +498,7 @@ cudaError_t scatter_by_splitters(const uint32_t *in, size_t n, const uint32_t *s
     const int grid = (int)std::min<size_t>(ntiles, (size_t)dev->sms * dev->occ_split);
     const int use_tma = (reinterpret_cast<uintptr_t>(in) & 15u) == 0;
     const SplitArg arg{splitters, nsplit};
-    if (g_bulk_exchange && dev->occ_split_bulk > 0) {
+    if (bulk) {
         auto kern = nsplit <= 1 ? KERNEL_SPLIT_BULK(1) : nsplit <= 3 ? KERNEL_SPLIT_BULK(3) : nsplit <= 7 ? KERNEL_SPLIT_BULK(7)
                                                                                                         : KERNEL_SPLIT_BULK(15);
         const int gridb = (int)std::min<size_t>(ntiles, (size_t)dev->sms * dev->occ_split_bulk);

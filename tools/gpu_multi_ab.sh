@@ -1,10 +1,11 @@
 #!/bin/bash
-# usage: gpu_multi_ab.sh N -- distributed bench with the bulk-copy and the LDS+STG splitter scatter
-N=${1:-2}
+# usage: gpu_multi_ab.sh N v_a v_b ... -- distributed bench (uniform) once per build variant under build/
+N=${1:-2}; shift
 mkdir -p gpurun_out
-( timeout 600 python -m pytest tests -m gpu -x -q -k "distrib or nccl or multi" > gpurun_out/pytest_multi_$N.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_multi_$N.log )
-for b in 1 0; do
-LIBSORT_BULK_EXCHANGE=$b timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29514 bench.py --gpus $N --steps 10 --warmup 3 > gpurun_out/bench_${N}gpu_bulk$b.json 2> gpurun_out/bench_${N}gpu_bulk$b.err
-tail -2 gpurun_out/bench_${N}gpu_bulk$b.err
+for v in "$@"; do
+LIBSORT_SO=$PWD/build/$v/libsort.so timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29514 bench.py --gpus $N --steps 10 --warmup 3 > gpurun_out/bench_${N}gpu_$v.json 2> gpurun_out/bench_${N}gpu_$v.err
+grep -h '^{' gpurun_out/bench_${N}gpu_$v.json | python -c "
+import json,sys
+for l in sys.stdin:
+    j=json.loads(l); print('$v', round(j['value'],1),'Gkeys/s', round(j['ms_per_step'],2),'ms', {k: round(x,3) for k,x in j['phases_ms'].items() if x is not None}, j['verify']['ok'])" || tail -3 gpurun_out/bench_${N}gpu_$v.err
 done
-tail -2 gpurun_out/pytest_multi_$N.log
