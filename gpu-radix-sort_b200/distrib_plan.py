@@ -71,3 +71,34 @@ def imbalance(totals):
     t = np.asarray(totals, dtype=np.float64)
     mean = t.mean() if t.size else 0.0
     return float(t.max() / mean) if mean > 0 else 1.0
+
+
+# ---- step-wise distributed LSD sort (DistributedSorter.sort_stepwise; k_step_bases / OUT_SLICED on the device) ----
+def step_bases(count_matrix, me):
+    """count_matrix[k][d] = keys of digit d on rank k.  After the step the whole array is bucket-major,
+    rank-minor (reference localTest/benchmarks.cpp:120-136, benchmark/pkg/sort/helpers.go:67-78), so rank
+    `me`'s first key of digit d goes to global position
+        sum over digits < d of every rank's count  +  sum over ranks < me of their digit-d count."""
+    c = np.asarray(count_matrix, dtype=np.int64)
+    per_digit = c.sum(axis=0)
+    return (np.cumsum(per_digit) - per_digit) + c[:me].sum(axis=0)
+
+
+def step_positions(keys, shift, nbits, bases):
+    """Global position of every key of this rank's slice after a step: bases[digit] + its rank among
+    the slice's keys of the same digit (stable).  Mirrors the OUT_SLICED scatter pass."""
+    k = np.asarray(keys, dtype=np.uint32)
+    d = ((k >> np.uint32(shift)) & np.uint32((1 << nbits) - 1)).astype(np.int64)
+    order = np.argsort(d, kind="stable")
+    counts = np.bincount(d, minlength=1 << nbits)
+    first = np.cumsum(counts) - counts
+    pos = np.empty(k.size, dtype=np.int64)
+    pos[order] = np.asarray(bases, dtype=np.int64)[d[order]] + (np.arange(k.size) - first[d[order]])
+    return pos
+
+
+def slice_of(positions, slice_starts):
+    """(owner, offset inside the owner's slice) of global positions; slice j holds [slice_starts[j], slice_starts[j+1])."""
+    starts = np.asarray(slice_starts, dtype=np.int64)
+    owner = np.searchsorted(starts[1:], positions, side="right")
+    return owner, np.asarray(positions, dtype=np.int64) - starts[owner]

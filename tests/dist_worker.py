@@ -61,6 +61,33 @@ def main():
             assert np.array_equal(mine, allkeys[start:start + mine.size]), kind
             if kind in ("fewvalues", "allequal"):
                 assert plan.imbalance(totals) < 1.1, (kind, totals)
+        # step-wise mode: counts -> all-gather -> bases -> every key to its global position's owner
+        for kind, lens in (("uniform", [n] * world), ("zipf", [n + 17 * r for r in range(world)]), ("allequal", [n] * world)):
+            mine = shard(rank, lens[rank], kind)
+            whole = np.concatenate([shard(r, lens[r], kind) for r in range(world)])
+            starts = np.concatenate([[0], np.cumsum(lens)])
+            for step in range(4):
+                digit = (mine >> np.uint32(8 * step)) & np.uint32(0xFF)
+                cnt = torch.from_numpy(np.bincount(digit, minlength=256).astype(np.int64))
+                rows = [torch.empty_like(cnt) for _ in range(world)]
+                dist.all_gather(rows, cnt)
+                bases = plan.step_bases(torch.stack(rows).numpy(), rank)
+                pos = plan.step_positions(mine, 8 * step, 8, bases)
+                owner, off = plan.slice_of(pos, starts)
+                sent = [(off[owner == r], mine[owner == r]) for r in range(world)]
+                everyone = [None] * world
+                dist.all_gather_object(everyone, sent)
+                nxt = np.zeros(lens[rank], dtype=np.uint32)
+                filled = 0
+                for src in range(world):
+                    o, v = everyone[src][rank]
+                    nxt[o] = v
+                    filled += len(o)
+                assert filled == lens[rank]
+                whole = whole[np.argsort((whole >> np.uint32(8 * step)) & np.uint32(0xFF), kind="stable")]
+                assert np.array_equal(nxt, whole[starts[rank]:starts[rank + 1]]), (kind, "step", step + 1)
+                mine = nxt
+            assert np.array_equal(mine, np.sort(whole)[starts[rank]:starts[rank + 1]])
         print("rank %d gloo plan ok" % rank)
     else:
         local = int(os.environ.get("LOCAL_RANK", "0"))

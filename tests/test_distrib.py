@@ -40,6 +40,14 @@ def test_plan_functions(pkg):
     assert np.bincount(d, minlength=4).max() <= 260                                                   # and balanced
     spl, thr = plan.choose_splitters(np.arange(1000, dtype=np.uint32), 4, with_ties=True)
     assert thr.tolist() == [0, 0, 0]                                                                  # no ties, no thresholds
+    # step-wise mode: bases are bucket-major, rank-minor; positions keep the slice's order inside a digit
+    cm = np.zeros((2, 256), dtype=np.int64)
+    cm[0, 1], cm[0, 3], cm[1, 1], cm[1, 2] = 2, 1, 1, 4
+    assert plan.step_bases(cm, 0)[[1, 2, 3]].tolist() == [0, 3, 7] and plan.step_bases(cm, 1)[[1, 2, 3]].tolist() == [2, 3, 8]
+    pos = plan.step_positions(np.array([3, 1, 1], np.uint32), 0, 8, plan.step_bases(cm, 0))
+    assert pos.tolist() == [7, 0, 1]
+    owner, off = plan.slice_of(np.array([0, 3, 4, 7]), [0, 4, 8])
+    assert owner.tolist() == [0, 0, 1, 1] and off.tolist() == [0, 3, 0, 3]
     off, tot = plan.recv_layout([[1, 2], [3, 4]])
     assert off.tolist() == [[0, 0], [1, 2]] and tot.tolist() == [4, 6]
     assert plan.imbalance([4, 6]) == pytest.approx(1.2)
