@@ -42,7 +42,8 @@ def measured_peak():
 
 
 class ClockSampler:
-    """nvidia-smi clocks/throttle reasons sampled DURING the timed region."""
+    """nvidia-smi clocks/throttle reasons sampled DURING the timed regions (device-timed loop, per-kernel
+    timing loop and the end-to-end loop, all of them the same sort back to back), every 25 ms."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
@@ -53,7 +54,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "25"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._pump, daemon=True)
             self.t.start()
@@ -64,15 +65,26 @@ class ClockSampler:
         for line in self.proc.stdout:
             self.lines.append(line.strip())
 
-    def stop(self):
+    def mark(self):
+        """Number of samples taken so far (to report a sub-region separately)."""
+        return len(self.lines)
+
+    def stop(self, first=None):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
+        time.sleep(0.05)
         self.proc.terminate()
         self.t.join(2)
+        out = self._summary(self.lines)
+        if first is not None:
+            out["device_loop"] = {k: v for k, v in self._summary(self.lines[:first]).items() if k in ("sm_mhz", "samples", "reasons")}
+        return out
+
+    @staticmethod
+    def _summary(lines):
         sm, mx, reasons = [], None, set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        for ln in lines:
             p = [x.strip() for x in ln.split(",")]
             if len(p) < 7:
                 continue
@@ -185,7 +197,7 @@ def run_single(args):
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / args.steps
-    clk = clocks.stop()
+    clk_mark = clocks.mark()
 
     # sortedness + multiset check of the last timed result (size-independent properties)
     out_u = d_out.view(torch.uint8).view(-1, 4)  # avoid signed compare: check via int64
@@ -232,6 +244,7 @@ def run_single(args):
     hw = h_work.numpy().view(np.uint32)
     assert bool(np.all(hw[1:] >= hw[:-1]))
     e2e_val = n * e2e_steps / t_e2e / 1e9
+    clk = clocks.stop(first=clk_mark)   # all timed regions; "device_loop" = the samples of the device-timed loop alone
 
     cpu_n = 1 << 26
     cpu_s, cpu_kind = time_cpu(h_keys[:cpu_n], 3)
