@@ -69,15 +69,18 @@ class ClockSampler:
         """Number of samples taken so far (to report a sub-region separately)."""
         return len(self.lines)
 
-    def stop(self, first=None):
+    def stop(self, first=0, loop_end=None):
+        """Summary of the samples from index `first` on; with loop_end, the samples [first, loop_end) -- taken
+        while the device-timed loop ran -- are summarised separately under "device_loop"."""
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.05)
         self.proc.terminate()
         self.t.join(2)
-        out = self._summary(self.lines)
-        if first is not None:
-            out["device_loop"] = {k: v for k, v in self._summary(self.lines[:first]).items() if k in ("sm_mhz", "samples", "reasons")}
+        out = self._summary(self.lines[first:])
+        if loop_end is not None:
+            out["device_loop"] = {k: v for k, v in self._summary(self.lines[first:loop_end]).items()
+                                  if k in ("sm_mhz", "samples", "reasons")}
         return out
 
     @staticmethod
@@ -179,6 +182,8 @@ def run_single(args):
     binding = pkg.binding
     binding.init_once()
     torch.cuda.set_device(0)
+    clocks = ClockSampler(0)
+    clocks.start()                      # nvidia-smi needs ~0.1 s before its first sample: started ahead of the set-up
     n = args.keys
     h_keys = pcg_keys(n)
     d_in = torch.from_numpy(h_keys.view(np.int32)).cuda()
@@ -187,10 +192,9 @@ def run_single(args):
     for _ in range(max(args.warmup, 3)):
         dev.sort(d_in, out=d_out, tmp=d_tmp)
     torch.cuda.synchronize()
-    clocks = ClockSampler(0)
-    clocks.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
+    clk_first = clocks.mark()
     e0.record()
     for _ in range(args.steps):
         dev.sort(d_in, out=d_out, tmp=d_tmp)   # input (1 GiB) is pristine every step and larger than L2
@@ -244,7 +248,7 @@ def run_single(args):
     hw = h_work.numpy().view(np.uint32)
     assert bool(np.all(hw[1:] >= hw[:-1]))
     e2e_val = n * e2e_steps / t_e2e / 1e9
-    clk = clocks.stop(first=clk_mark)   # all timed regions; "device_loop" = the samples of the device-timed loop alone
+    clk = clocks.stop(first=clk_first, loop_end=clk_mark)   # all timed regions; "device_loop": the device-timed loop alone
 
     cpu_n = 1 << 26
     cpu_s, cpu_kind = time_cpu(h_keys[:cpu_n], 3)
@@ -283,32 +287,34 @@ def run_multi(args, rank, world, local_rank):
     dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank), timeout=datetime.timedelta(seconds=180))
     n = args.keys
     # one continuous PCG stream; rank g owns elements [g*n, (g+1)*n)  
+    clocks = ClockSampler(local_rank)
+    clocks.start()                      # live well before the timed loop (set-up below takes seconds)
     d_in = distrib.shard_of_pcg_stream(rank, n, args.dist)
     sorter = distrib.DistributedSorter(n, dist.group.WORLD, mode=args.exchange)
     if args.algo == "stepwise":
-        run_multi_stepwise(args, rank, world, local_rank, sorter, d_in)
+        run_multi_stepwise(args, rank, world, local_rank, sorter, d_in, clocks)
         return
     for _ in range(max(args.warmup, 3)):
         sorter.sort(d_in)
     torch.cuda.synchronize()
     dist.barrier()
-    clocks = ClockSampler(local_rank)
-    clocks.start()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    clk_first = clocks.mark()
     e0.record()
     for _ in range(args.steps):
         out, cnt = sorter.sort(d_in)
     e1.record()
     torch.cuda.synchronize()
+    clk_end = clocks.mark()
     dist.barrier()
     ms_local = torch.tensor([e0.elapsed_time(e1) / args.steps], device="cuda")
     dist.all_reduce(ms_local, op=dist.ReduceOp.MAX)
     ms = float(ms_local.item())
-    clk = clocks.stop()
     stats = sorter.verify(d_in, out, cnt)           # sortedness, rank ordering, multiset fingerprint
     phases = sorter.phase_times(d_in)               # per-phase CUDA-event times, max over ranks
     e2e = sorter.e2e(args, d_in)                    # collective: every rank takes part
+    clk = clocks.stop(first=clk_first, loop_end=clk_end)
     if rank == 0:
         peak, peak_src = measured_peak()
         total = n * world
@@ -336,7 +342,7 @@ def run_multi(args, rank, world, local_rank):
     dist.destroy_process_group()
 
 
-def run_multi_stepwise(args, rank, world, local_rank, sorter, d_in):
+def run_multi_stepwise(args, rank, world, local_rank, sorter, d_in, clocks):
     """--algo stepwise: the reference's own distributed algorithm (one exchange per 8-bit step) on the
     NVLink backend, beside the default single-exchange sort -- the like-for-like number."""
     import torch
@@ -346,20 +352,20 @@ def run_multi_stepwise(args, rank, world, local_rank, sorter, d_in):
         sorter.sort_stepwise(d_in)
     torch.cuda.synchronize()
     dist.barrier()
-    clocks = ClockSampler(local_rank)
-    clocks.start()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    clk_first = clocks.mark()
     e0.record()
     for _ in range(args.steps):
         out, cnt = sorter.sort_stepwise(d_in)
     e1.record()
     torch.cuda.synchronize()
+    clk_end = clocks.mark()
     dist.barrier()
     ms_local = torch.tensor([e0.elapsed_time(e1) / args.steps], device="cuda")
     dist.all_reduce(ms_local, op=dist.ReduceOp.MAX)
     ms = float(ms_local.item())
-    clk = clocks.stop()
+    clk = clocks.stop(first=clk_first, loop_end=clk_end)
     stats = sorter.verify(d_in, out, cnt)
     marks = []
 
