@@ -175,3 +175,82 @@ def test_direct_invoke_sorts_request(pkg, da, tmp_path):
     order = np.argsort((fed >> 8) & 0xFF, kind="stable")
     assert np.array_equal(got, fed[order])                            # stable partial sort of exactly the requested slices
     assert out.shape.caps == (np.bincount((fed >> 8) & 0xFF, minlength=256) * 4).tolist()
+
+
+# ---- the reference's distributed sort over file arrays (benchmark/pkg/sort: BucketReader, SortDistribFromArr) ----
+@pytest.fixture()
+def dfiles(pkg):
+    return importlib.import_module(pkg.__name__ + ".distrib_files")
+
+
+def numpy_worker(da):
+    """Stand-in for faas.f on machines without a GPU: the same request handling, numpy as the sorter."""
+    def work(req):
+        try:
+            raw = da.readPartRefs(da.getPartRefs(req))
+            keys = np.frombuffer(bytes(raw), np.uint32)
+            digit = (keys >> np.uint32(req["offset"])) & np.uint32((1 << req["width"]) - 1)
+            counts = np.bincount(digit, minlength=1 << req["width"])
+            da.writeOutput(req, keys[np.argsort(digit, kind="stable")].tobytes(), (np.cumsum(counts) - counts).tolist())
+        except Exception as e:  # noqa: BLE001
+            return {"success": False, "err": str(e)}
+        return {"success": True, "err": ""}
+    return work
+
+
+def test_bucket_reader_orders(da, dfiles, tmp_path):
+    """helpers.go:30-140 / distrib_test.go:54-149: STRIDED = bucket-major, INORDER = array-major; refs cut at any byte."""
+    arrs, bufs = [], []
+    for a in range(3):
+        arr = da.fileDistribArray.Create(tmp_path / ("a%d" % a), da.ArrayShape.fromCaps([8, 0, 12, 4]))
+        parts = [bytes([16 * a + p] * n) for p, n in enumerate([8, 0, 10, 4])]      # partition 2 only partly filled
+        for p, b in enumerate(parts):
+            arr.WritePart(p, b)
+        arrs.append(arr)
+        bufs.append(parts)
+    strided = b"".join(bufs[a][p] for p in range(4) for a in range(3))
+    inorder = b"".join(bufs[a][p] for a in range(3) for p in range(4))
+    assert bytes(dfiles.BucketReader(arrs, dfiles.STRIDED).read()) == strided
+    assert bytes(dfiles.BucketReader(arrs, dfiles.INORDER).read()) == inorder
+    r = dfiles.BucketReader(arrs, dfiles.STRIDED)
+    got, sizes = b"", []
+    while True:
+        refs = r.readRef(7)                                       # slices that straddle partitions and arrays
+        if not refs:
+            break
+        sizes.append(sum(x.nbyte for x in refs))
+        got += bytes(da.readPartRefs(refs))
+    assert got == strided and all(s == 7 for s in sizes[:-1]) and sizes[-1] == len(strided) - 7 * (len(sizes) - 1)
+    assert dfiles.BucketReader([], dfiles.STRIDED).readRef(10) == []
+    with pytest.raises(ValueError):
+        dfiles.BucketReader(arrs, 7)
+
+
+@pytest.mark.parametrize("nworker,width,n", [(2, 8, 5000), (3, 8, 4099), (2, 16, 3000), (1, 4, 257)])
+def test_sort_distrib_over_files_numpy_worker(da, dfiles, tmp_path, nworker, width, n):
+    """SortDistribFromRaw (distrib.go:183-248) end to end with the numpy stand-in worker: the orchestration,
+    the request format and the file exchange; nothing is left behind under the mount."""
+    da.SetDistribMount(tmp_path)
+    keys = np.random.default_rng(n).integers(0, 1 << 32, n, dtype=np.uint64).astype(np.uint32)
+    keys[::7] = keys[0]
+    out = dfiles.SortDistribFromRaw(keys.tobytes(), "t", nworker=nworker, width=width, worker=numpy_worker(da))
+    assert np.array_equal(np.frombuffer(bytes(out), np.uint32), np.sort(keys))
+    assert list(tmp_path.iterdir()) == []
+
+
+def test_sort_distrib_worker_failure_is_reported(da, dfiles, tmp_path):
+    da.SetDistribMount(tmp_path)
+    with pytest.raises(RuntimeError, match="Worker failure on step 0, worker 1: boom"):
+        dfiles.SortDistribFromRaw(np.arange(100, dtype=np.uint32).tobytes(), "f", nworker=2,
+                                  worker=lambda req: {"success": not req["output"].endswith("worker1_output"), "err": "boom"},
+                                  parallel=False)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nworker,width", [(2, 8), (3, 16)])
+def test_sort_distrib_over_files_gpu_worker(pkg, da, dfiles, tmp_path, nworker, width):
+    """The same path with the real worker (faas.f -> gpuPartial), workers on concurrent threads."""
+    da.SetDistribMount(tmp_path)
+    keys = np.random.default_rng(3).integers(0, 1 << 32, 200003, dtype=np.uint64).astype(np.uint32)
+    out = dfiles.SortDistribFromRaw(keys.tobytes(), "g", nworker=nworker, width=width)
+    assert np.array_equal(np.frombuffer(bytes(out), np.uint32), np.sort(keys))
