@@ -257,6 +257,31 @@ def getOutputArray(req, shape):
     raise ValueError("Invalid request type: " + str(req["arrType"]))
 
 
+def exactBoundaries(buf, boundaries, offset, width):
+    """Group boundaries as the reference's contract defines them (exclusive prefix sums of the group
+    sizes; localTest/tests.cpp:44-68, faasTest/pylibsort/sort.py:67-91) from what gpuPartial returned.
+
+    The reference's implementation -- which gpuPartial reproduces bit for bit -- deviates from that
+    contract when the lowest groups are empty or group 1 is (libsort/sort.cu:14-27: thread 0 never
+    writes; 381-387: the back-fill stops at group 2), e.g. it reports boundaries[1] == 0 although
+    group 0 holds keys.  Consumers that cut the buffer into per-group partitions need the contract.
+    O(number of groups): with g0 the group of the first sorted key, every boundary up to g0 is 0,
+    boundaries above max(g0, 1) are already right, and boundaries[1] equals boundaries[2] when group 1
+    is empty."""
+    nElem = int(len(buf) / 4)
+    out = [int(b) for b in boundaries]
+    ngroups = len(out)
+    if nElem == 0 or ngroups == 0:
+        return [0] * ngroups
+    first = int(np.frombuffer(memoryview(buf).cast("B")[:4], dtype=np.uint32)[0])
+    g0 = (first >> offset) & ((1 << width) - 1)
+    for g in range(min(g0 + 1, ngroups)):
+        out[g] = 0
+    if g0 == 0 and ngroups > 1 and out[1] == 0:       # group 1 is empty: it starts where group 2 starts
+        out[1] = out[2] if ngroups > 2 else nElem
+    return out
+
+
 def writeOutput(req, rawBytes, boundaries):
     """Store a partially sorted buffer as the request's output array: one partition per bucket, bucket
     g spanning [4*boundaries[g], 4*boundaries[g+1]) (reference data.py:289-298)."""

@@ -32,6 +32,10 @@ def f(event):
         keep, raw = _pinned_buffer(sum(r.nbyte for r in refs))
         pylibsort.readPartRefs(refs, dest=raw)
         boundaries = pylibsort.sortPartial(raw, event["offset"], event["width"])
+        # gpuPartial is bit-exact with the reference, boundary quirks included; the
+        # output partitions follow the contract (one partition per group, sized by the group), which is
+        # what the consumers of these arrays -- BucketReader, checkPartial, CheckPartialArray -- rely on
+        boundaries = pylibsort.exactBoundaries(raw, boundaries, event["offset"], event["width"])
     except Exception as e:  # noqa: BLE001 -- the protocol reports every failure in-band
         return {"success": False, "err": str(e)}
     pylibsort.writeOutput(event, raw, boundaries)

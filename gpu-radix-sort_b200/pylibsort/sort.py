@@ -4,6 +4,7 @@ import ctypes
 import numpy as np
 
 from .. import binding
+from ..distrib_array import exactBoundaries  # noqa: F401  (pure Python; re-exported under pylibsort)
 
 
 class sortException(Exception):

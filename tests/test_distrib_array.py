@@ -254,3 +254,45 @@ def test_sort_distrib_over_files_gpu_worker(pkg, da, dfiles, tmp_path, nworker, 
     keys = np.random.default_rng(3).integers(0, 1 << 32, 200003, dtype=np.uint64).astype(np.uint32)
     out = dfiles.SortDistribFromRaw(keys.tobytes(), "g", nworker=nworker, width=width)
     assert np.array_equal(np.frombuffer(bytes(out), np.uint32), np.sort(keys))
+
+
+def test_exact_boundaries_from_reference_quirks(da, oracle):
+    """exactBoundaries() turns what gpuPartial returns (the reference's gpu_groups + back-fill, quirks
+    included: oracle.gpu_partial) into the contract's boundaries (oracle.boundaries_exact) for every
+    skew that triggers a quirk -- lowest groups empty, group 1 empty, single group, single key."""
+    x = oracle.pcg_stream(30000)
+    cases = {"uniform": x, "nogroup0": x | np.uint32(0x01010101), "nogroup1": x & ~np.uint32(0x01010101),
+             "zeros": np.zeros(500, np.uint32), "ones": np.full(777, 0xFFFFFFFF, np.uint32),
+             "few": (x % np.uint32(3)) * np.uint32(0x00010001), "sparse": x[:40], "high": x | np.uint32(0xF0F0F0F0),
+             "one": np.array([0x00020000], np.uint32)}
+    quirky = 0
+    for name, k in cases.items():
+        k = np.ascontiguousarray(k, dtype=np.uint32)
+        for off, w in ((0, 8), (8, 8), (16, 16), (0, 16), (4, 2), (24, 8), (3, 12), (30, 2)):
+            out, b = oracle.gpu_partial(k, off, w)
+            want = oracle.boundaries_exact(k, off, w).tolist()
+            quirky += b.tolist() != want
+            assert da.exactBoundaries(out.tobytes(), b.tolist(), off, w) == want, (name, off, w)
+    assert quirky > 10                                             # the inputs really exercise the deviations
+    assert da.exactBoundaries(b"", [0, 0, 0, 0], 0, 2) == [0, 0, 0, 0]
+
+
+def test_sort_distrib_over_files_survives_boundary_quirks(da, dfiles, oracle, tmp_path):
+    """With 16-bit steps most groups are empty; partitions cut at the reference's quirky boundaries put
+    keys into the wrong bucket and the regather loses stability (this input sorts wrong that way).  The
+    worker's repair (exactBoundaries, as faas.f applies it) restores the contract."""
+    da.SetDistribMount(tmp_path)
+    keys = np.random.default_rng(3).integers(0, 1 << 32, 200003, dtype=np.uint64).astype(np.uint32)
+
+    def worker(repair):
+        def work(req):
+            raw = da.readPartRefs(da.getPartRefs(req))
+            out, b = oracle.gpu_partial(np.frombuffer(bytes(raw), np.uint32), req["offset"], req["width"])
+            b = da.exactBoundaries(out.tobytes(), b.tolist(), req["offset"], req["width"]) if repair else b.tolist()
+            da.writeOutput(req, out.tobytes(), b)
+            return {"success": True, "err": ""}
+        return work
+    good = dfiles.SortDistribFromRaw(keys.tobytes(), "r", nworker=3, width=16, worker=worker(True), parallel=False)
+    assert np.array_equal(np.frombuffer(bytes(good), np.uint32), np.sort(keys))
+    bad = dfiles.SortDistribFromRaw(keys.tobytes(), "q", nworker=3, width=16, worker=worker(False), parallel=False)
+    assert not np.array_equal(np.frombuffer(bytes(bad), np.uint32), np.sort(keys))     # what the quirk costs
