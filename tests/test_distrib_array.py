@@ -246,16 +246,6 @@ def test_sort_distrib_worker_failure_is_reported(da, dfiles, tmp_path):
                                   parallel=False)
 
 
-@pytest.mark.gpu
-@pytest.mark.parametrize("nworker,width", [(2, 8), (3, 16)])
-def test_sort_distrib_over_files_gpu_worker(pkg, da, dfiles, tmp_path, nworker, width):
-    """The same path with the real worker (faas.f -> gpuPartial), workers on concurrent threads."""
-    da.SetDistribMount(tmp_path)
-    keys = np.random.default_rng(3).integers(0, 1 << 32, 200003, dtype=np.uint64).astype(np.uint32)
-    out = dfiles.SortDistribFromRaw(keys.tobytes(), "g", nworker=nworker, width=width)
-    assert np.array_equal(np.frombuffer(bytes(out), np.uint32), np.sort(keys))
-
-
 def test_exact_boundaries_from_reference_quirks(da, oracle):
     """exactBoundaries() turns what gpuPartial returns (the reference's gpu_groups + back-fill, quirks
     included: oracle.gpu_partial) into the contract's boundaries (oracle.boundaries_exact) for every
