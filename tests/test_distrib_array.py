@@ -286,3 +286,31 @@ def test_sort_distrib_over_files_survives_boundary_quirks(da, dfiles, oracle, tm
     assert np.array_equal(np.frombuffer(bytes(good), np.uint32), np.sort(keys))
     bad = dfiles.SortDistribFromRaw(keys.tobytes(), "q", nworker=3, width=16, worker=worker(False), parallel=False)
     assert not np.array_equal(np.frombuffer(bytes(bad), np.uint32), np.sort(keys))     # what the quirk costs
+
+
+def test_golden_arrays_written_by_the_reference(da, tmp_path):
+    """tests/golden/arrays/* were written by the reference's own faasTest/pylibsort/data.py
+    (tests/golden/make_golden_arrays.py, which also checked that the reference reads OUR arrays).
+    Ours must read them back exactly and, for the same operations, write byte-identical files."""
+    import shutil
+    gold = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "arrays")
+    want = json.load(open(os.path.join(gold, "expected.json")))
+    shutil.copytree(gold, tmp_path / "arrays")
+    for name, exp in want.items():
+        arr = da.fileDistribArray.Open(tmp_path / "arrays" / name)
+        assert arr.shape.caps == exp["caps"] and arr.shape.lens == exp["lens"], name
+        assert [bytes(arr.ReadPart(p)).hex() for p in range(arr.shape.npart)] == exp["parts"], name
+    # the same operations through our writer: identical bytes on disk
+    exp = want["partial"]
+    parts = [bytes.fromhex(h) for h in exp["parts"]]
+    mine = da.fileDistribArray.Create(tmp_path / "mine", da.ArrayShape.fromCaps(exp["caps"]))
+    mine.WritePart(0, parts[0][:4])
+    mine.WritePart(3, parts[3])
+    mine.WritePart(0, parts[0][4:])
+    mine.WritePart(1, parts[1])
+    mine.Close()
+    da.SetDistribMount(tmp_path)
+    da.writeOutput({"arrType": "file", "output": "b"}, bytes.fromhex(want["buckets"]["sorted"]), want["buckets"]["boundaries"])
+    for ours, theirs in (("mine", "partial"), ("b", "buckets")):
+        for f in ("meta.json", "data.dat"):
+            assert open(tmp_path / ours / f, "rb").read() == open(os.path.join(gold, theirs, f), "rb").read(), (ours, f)
