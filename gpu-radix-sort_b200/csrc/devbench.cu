@@ -163,6 +163,20 @@ static int run_time(size_t n, int reps, const char *dist)
                n / ms / 1e6, c.bytes_per_key * n / ms / 1e6, t.memset_ms, t.histogram_ms, t.scan_ms);
         for (int p = 0; p < t.npass; p++) printf(" %.3f", t.pass_ms[p]);
         printf(" (pass0 %.0f GB/s) bounds %.3f launches %d\n", 8.0 * n / t.pass_ms[0] / 1e6, t.boundaries_ms, t.launches);
+        if (c.width == 32) {
+            // cheap full-size check of the timed configuration: ascending + same multiset fingerprint
+            std::vector<uint32_t> got(n);
+            CHECK(cudaMemcpy(got.data(), d.out, n * 4, cudaMemcpyDeviceToHost));
+            uint64_t s0 = 0, s1 = 0, x0 = 0, x1 = 0;
+            size_t bad = 0;
+            for (size_t i = 0; i < n; i++) {
+                s0 += h[i]; x0 ^= (uint64_t)h[i] * 0x9E3779B97F4A7C15ull;
+                s1 += got[i]; x1 ^= (uint64_t)got[i] * 0x9E3779B97F4A7C15ull;
+                if (i && got[i - 1] > got[i]) bad++;
+            }
+            printf("verify full32: %s (descents %zu, sum %s, xor %s)\n", (!bad && s0 == s1 && x0 == x1) ? "OK" : "FAIL", bad,
+                   s0 == s1 ? "ok" : "DIFF", x0 == x1 ? "ok" : "DIFF");
+        }
     }
     return 0;
 }

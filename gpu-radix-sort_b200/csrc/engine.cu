@@ -2,6 +2,8 @@
 #include "engine.cuh"
 #include "kernels.cuh"
 #include "onesweep_bulk.cuh"
+#include "scatter2.cuh"
+#include "scatter3.cuh"
 
 #include <algorithm>
 #include <atomic>
@@ -76,6 +78,57 @@ constexpr int kTileSplitBulk = SORT_THREADS * SPLIT_KPT;
 using SmemSlicedA = OnesweepSmem<SORT_THREADS, SORT_KPT, OUT_SLICED, RadixBinner::Arg>;
 using SmemSlicedB = OnesweepSmem<SORT_THREADS, BALLOT_KPT, OUT_SLICED, RadixBinner::Arg>;
 
+// ---- second-generation scatter pass (scatter2.cuh): developer-selectable variants ----------
+typedef void (*Scatter2Fn)(const uint32_t *, uint32_t *, uint32_t, RadixBinner::Arg, const uint32_t *, uint32_t *, uint32_t *,
+                           uint32_t *, uint32_t, int);
+struct K3Variant {
+    const char *name;
+    Scatter2Fn fn;
+    int threads, tile;
+    size_t smem;
+};
+#define K3V(NAME, T, K, M, LBW, LD, RG, E, PF) \
+    {NAME, k_scatter2<T, K, M, LBW, LD, RG, E, PF>, T, (T) * (K), sizeof(Scatter2Smem<T, K, LD, RadixBinner::Arg>)}
+#define K3P(NAME, K, LBW, BATCH, PF, WO) {NAME, k_scatter3<K, LBW, BATCH, PF, WO>, S3_THREADS, S3_COMPUTE * (K), sizeof(Scatter3Smem<K>)}
+static const K3Variant g_k3[] = {
+    K3V("ldg256x56p", 256, 56, 3, 4, LOAD_LDG, RAG_PAIR, false, true),
+    K3V("ldg256x56m", 256, 56, 3, 4, LOAD_LDG, RAG_MASK, false, true),
+    K3V("ldg256x56s", 256, 56, 3, 4, LOAD_LDG, RAG_SCALAR, false, true),
+    K3V("ldg256x56p_nopf", 256, 56, 3, 4, LOAD_LDG, RAG_PAIR, false, false),
+    K3V("ldg256x56p_lb8", 256, 56, 3, 8, LOAD_LDG, RAG_PAIR, false, true),
+    K3V("inp256x56p", 256, 56, 3, 4, LOAD_TMA_INPLACE, RAG_PAIR, false, true),
+    K3V("inp256x56p_nopf", 256, 56, 3, 4, LOAD_TMA_INPLACE, RAG_PAIR, false, false),
+    K3V("inp256x56m", 256, 56, 3, 4, LOAD_TMA_INPLACE, RAG_MASK, false, true),
+    K3V("sep512x22p", 512, 22, 2, 4, LOAD_TMA_SEP, RAG_PAIR, true, false),
+    K3V("sep512x22p_late", 512, 22, 2, 4, LOAD_TMA_SEP, RAG_PAIR, false, true),
+    K3V("sep512x22m", 512, 22, 2, 4, LOAD_TMA_SEP, RAG_MASK, true, false),
+    K3V("sep512x22p_lb8", 512, 22, 2, 8, LOAD_TMA_SEP, RAG_PAIR, true, false),
+    K3V("sep384x30p", 384, 30, 2, 4, LOAD_TMA_SEP, RAG_PAIR, true, false),
+    K3V("ldg512x28p", 512, 28, 2, 4, LOAD_LDG, RAG_PAIR, false, true),
+    K3V("ldg256x40p", 256, 40, 4, 4, LOAD_LDG, RAG_PAIR, false, true),
+    K3V("ldg256x48p", 256, 48, 3, 4, LOAD_LDG, RAG_PAIR, false, true),
+    K3P("pipe44", 44, 4, 4, true, 0),
+    K3P("pipe44w", 44, 4, 4, true, 1),
+    K3P("pipe44w_b2", 44, 4, 2, true, 1),
+    K3P("pipe44w_lb8", 44, 8, 4, true, 1),
+    K3P("pipe42w", 42, 4, 2, true, 1),
+    K3P("pipe40w", 40, 4, 4, true, 1),
+    K3P("pipe36w", 36, 4, 4, true, 1),
+};
+constexpr int kNumK3 = (int)(sizeof(g_k3) / sizeof(g_k3[0]));
+static int k3_selected()
+{
+    static const int sel = [] {
+        const char *e = getenv("LIBSORT_K3");
+        if (!e || !*e) return -1;
+        for (int i = 0; i < kNumK3; i++)
+            if (!strcmp(e, g_k3[i].name)) return i;
+        fprintf(stderr, "libsort: unknown LIBSORT_K3=%s\n", e);
+        return -1;
+    }();
+    return sel;
+}
+
 
 
 // workspace layout, in uint32 words
@@ -107,6 +160,7 @@ struct DevInfo {
     int sms = 0;
     int occ_a = 0, occ_b = 0, occ_split = 0, occ_bulk = 0, occ_split_bulk = 0;  // resident CTAs per SM of the three scatter kernels
     int occ_sliced_a = 0, occ_sliced_b = 0;
+    int occ_k3[32] = {};
     int hist_occ = 0;
     bool rank_atoms = false;  // rank keys with returning shared atomics (self-tested) instead of ballots
 };
@@ -230,6 +284,12 @@ static cudaError_t dev_info(DevInfo **out)
                                                           HIST_THREADS, 0);
         if (e != cudaSuccess) return e;
         if (d.occ_a < 1 || d.occ_b < 1 || d.occ_split < 1 || d.hist_occ < 1) return cudaErrorLaunchOutOfResources;
+        for (int i = 0; i < kNumK3; i++) {
+            e = cudaFuncSetAttribute((const void *)g_k3[i].fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_k3[i].smem);
+            if (e != cudaSuccess) { d.occ_k3[i] = 0; (void)cudaGetLastError(); continue; }
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.occ_k3[i], (const void *)g_k3[i].fn, g_k3[i].threads, g_k3[i].smem);
+            if (e != cudaSuccess) { d.occ_k3[i] = 0; (void)cudaGetLastError(); }
+        }
         e = choose_rank_mode(dev, &d.rank_atoms);
         if (e != cudaSuccess) return e;
         if (const char *dbg = getenv("LIBSORT_DEBUG"))
@@ -237,6 +297,10 @@ static cudaError_t dev_info(DevInfo **out)
                 fprintf(stderr, "libsort: dev %d sms=%d rank=%s tiles A/B=%d/%d occ A/B/split=%d/%d/%d hist_occ=%d smem A/B=%zu/%zu\n", dev,
                         d.sms, d.rank_atoms ? "atoms" : "ballot", kTileA, kTileB, d.occ_a, d.occ_b, d.occ_split, d.hist_occ,
                         sizeof(SmemA), sizeof(SmemB));
+        if (const char *dbg = getenv("LIBSORT_DEBUG"))
+            if (dbg[0] == '1' && k3_selected() >= 0)
+                fprintf(stderr, "libsort: dev %d K3 variant %s tile=%d smem=%zu occ=%d\n", dev, g_k3[k3_selected()].name,
+                        g_k3[k3_selected()].tile, g_k3[k3_selected()].smem, d.occ_k3[k3_selected()]);
         d.ready = true;
     }
     *out = &d;
@@ -246,7 +310,10 @@ static cudaError_t dev_info(DevInfo **out)
 int tile_keys()
 {
     DevInfo *dev = nullptr;  // the tile of the kernels this device runs (atomic or ballot ranking)
-    return (dev_info(&dev) == cudaSuccess && !dev->rank_atoms) ? kTileB : kTileA;
+    if (dev_info(&dev) != cudaSuccess) return kTileA;
+    const int k3 = k3_selected();
+    if (dev->rank_atoms && k3 >= 0 && dev->occ_k3[k3] > 0) return g_k3[k3].tile;
+    return dev->rank_atoms ? kTileA : kTileB;
 }
 
 static PassPlan make_plan(uint32_t offset, uint32_t width)
@@ -347,7 +414,8 @@ cudaError_t sort_bits(const uint32_t *in, uint32_t *a, uint32_t *b, uint32_t *wa
     CK(dev_info(&dev));
     uint32_t *ws = static_cast<uint32_t *>(workspace);
     uint32_t *ghist = ws + WS_HIST, *base = ws + WS_BASE, *tickets = ws + WS_TICKET, *desc = ws + WS_DESC;
-    const int tile = dev->rank_atoms ? kTileA : kTileB;
+    const int k3 = (dev->rank_atoms && k3_selected() >= 0 && dev->occ_k3[k3_selected()] > 0) ? k3_selected() : -1;
+    const int tile = k3 >= 0 ? g_k3[k3].tile : dev->rank_atoms ? kTileA : kTileB;
     const size_t ntiles = num_tiles(n, tile);
     const uint32_t ptiles = portion_tiles(tile);
     const size_t nportions = (ntiles + ptiles - 1) / ptiles;
@@ -398,7 +466,11 @@ cudaError_t sort_bits(const uint32_t *in, uint32_t *a, uint32_t *b, uint32_t *wa
             const bool full_digit = plan.mask[p] == 0xffu;
             const RadixBinner::Arg barg{plan.shift[p], plan.mask[p]};
             uint32_t *dsc = desc + ((size_t)p * ntiles + t0) * RADIX, *tk = tickets + p * MAX_PORTIONS + q;
-            if (dev->rank_atoms && g_bulk_out && dev->occ_bulk > 0) {
+            if (k3 >= 0) {
+                const int gridk = (int)std::min<size_t>(nt, (size_t)dev->sms * dev->occ_k3[k3]);
+                g_k3[k3].fn<<<gridk, g_k3[k3].threads, g_k3[k3].smem, st>>>(src + k0, dst, (uint32_t)(k1 - k0), barg, bcur, bnext, dsc, tk,
+                                                                           nt, use_tma);
+            } else if (dev->rank_atoms && g_bulk_out && dev->occ_bulk > 0) {
                 const int gridb = (int)std::min<size_t>(nt, (size_t)dev->sms * dev->occ_bulk);
                 KERNEL_BULK<<<gridb, SORT_THREADS, sizeof(SmemBulk), st>>>(src + k0, dst, (uint32_t)(k1 - k0), barg, bcur, bnext, dsc, tk,
                                                                           nt, use_tma);
