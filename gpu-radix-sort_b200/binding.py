@@ -13,7 +13,8 @@ ADDITIVE_SYMBOLS = ["libsortTileKeys", "libsortWorkspaceBytes", "libsortDeviceSo
                     "libsortReleaseCaches", "libsortErrorString", "libsortDebugSetPortionTiles",
                     "libsortDeviceSample", "libsortDevicePickSplitters", "libsortDeviceSplitCounts", "libsortPopulateInputAt", "libsortDeviceScatterToPeers",
                     "libsortIpcAlloc", "libsortIpcFree", "libsortIpcExport", "libsortIpcOpen", "libsortIpcClose", "libsortDistribSort",
-                    "libsortStepTableBytes", "libsortStepTableInit", "libsortStepCounts", "libsortStepBases", "libsortStepScatter"]
+                    "libsortStepTableBytes", "libsortStepTableInit", "libsortStepCounts", "libsortStepBases", "libsortStepScatter",
+                    "libsortRankAudit", "libsortDeviceExchangePlanned", "libsortDeviceSortDyn"]
 
 BOUNDS_REFERENCE = 0
 BOUNDS_EXACT = 1
@@ -97,6 +98,12 @@ def lib():
     for name in ("libsortDeviceSample", "libsortDevicePickSplitters", "libsortDeviceSplitCounts", "libsortPopulateInputAt", "libsortDeviceScatterToPeers", "libsortIpcAlloc",
                  "libsortIpcFree", "libsortIpcExport", "libsortIpcOpen", "libsortIpcClose"):
         getattr(L, name).restype = ci
+    L.libsortRankAudit.argtypes = [vp]
+    L.libsortRankAudit.restype = ci
+    L.libsortDeviceExchangePlanned.argtypes = [vp, sz, vp, ci, ci, vp, vp, sz, vp, vp, vp, sz, vp]
+    L.libsortDeviceExchangePlanned.restype = ci
+    L.libsortDeviceSortDyn.argtypes = [vp, vp, vp, sz, vp, vp, sz, vp, ctypes.POINTER(KernelTimes)]
+    L.libsortDeviceSortDyn.restype = ci
     L.libsortDistribSort.argtypes = [vp, sz, ci]
     L.libsortDistribSort.restype = ci
     L.libsortStepTableBytes.argtypes = []

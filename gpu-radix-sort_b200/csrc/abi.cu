@@ -239,11 +239,18 @@ int host_sort(uint32_t *h_keys, size_t n, uint32_t offset, uint32_t width, uint3
         return 1;
     }
     if (!ensure_capacity(c, n, ngroups)) return 0;
-    if (!c.copier.to_device(c.a, h_keys, n * sizeof(uint32_t), c.stream)) return 0;
     uint32_t *res = nullptr;
-    cudaError_t e = sort_bits(c.a, c.a, c.b, nullptr, n, offset, width, h_bounds ? c.d_bounds : nullptr,
-                              boundary_mode_from_env(), c.ws, c.ws_cap, c.stream, &res, nullptr);
-    if (!cuda_ok(e, "sort")) return 0;
+    for (int attempt = 0; attempt < 2; attempt++) {
+        if (!c.copier.to_device(c.a, h_keys, n * sizeof(uint32_t), c.stream)) return 0;
+        cudaError_t e = sort_bits(c.a, c.a, c.b, nullptr, n, offset, width, h_bounds ? c.d_bounds : nullptr,
+                                  boundary_mode_from_env(), c.ws, c.ws_cap, c.stream, &res, nullptr);
+        if (!cuda_ok(e, "sort")) return 0;
+        // the caller's keys are still intact: if the atomic-ranking audit tripped, sort them again
+        // with the ballot kernels before anything is copied back
+        bool violated = false;
+        if (!cuda_ok(rank_audit(c.stream, &violated), "rank audit")) return 0;
+        if (!violated) break;
+    }
     if (!c.copier.to_host(h_keys, res, n * sizeof(uint32_t), c.stream)) return 0;
     if (h_bounds &&
         !cuda_ok(cudaMemcpyAsync(h_bounds, c.d_bounds, ngroups * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream),
@@ -354,6 +361,14 @@ API int libsortDeviceSort(const uint32_t *d_in, uint32_t *d_out, uint32_t *d_tmp
     return (int)e;
 }
 
+API int libsortRankAudit(void *stream)
+{
+    bool violated = false;
+    cudaError_t e = rank_audit((cudaStream_t)stream, &violated);
+    if (e != cudaSuccess) return -(int)e - 100;
+    return violated ? 1 : 0;
+}
+
 API int libsortDeviceCount(void)
 {
     std::lock_guard<std::mutex> lk(g_pool.mu);
@@ -432,6 +447,24 @@ API int libsortDeviceScatterToPeers(const uint32_t *d_in, size_t n, const uint32
 {
     return (int)scatter_by_splitters(d_in, n, splitters, nsplit, dest_ptrs, d_workspace, workspace_len,
                                      (cudaStream_t)stream);
+}
+
+API int libsortDeviceExchangePlanned(const uint32_t *d_in, size_t n, const uint32_t *splitters, int nranks, int me,
+                                     const uint32_t *d_count_matrix, const unsigned long long *d_peer_bases, size_t cap,
+                                     uint32_t *d_nrecv, uint32_t *d_status, void *d_workspace, size_t workspace_len,
+                                     void *stream)
+{
+    return (int)exchange_planned(d_in, n, splitters, nranks, me, d_count_matrix, d_peer_bases, cap, d_nrecv, d_status,
+                                 d_workspace, workspace_len, (cudaStream_t)stream);
+}
+
+API int libsortDeviceSortDyn(const uint32_t *d_in, uint32_t *d_out, uint32_t *d_tmp, size_t capacity, const uint32_t *d_n,
+                             void *d_workspace, size_t workspace_len, void *stream, LibsortKernelTimes *times)
+{
+    if (!d_in || !d_out || !d_tmp || !d_n || d_tmp == d_out || d_tmp == d_in || capacity == 0) return -1;
+    uint32_t *res = nullptr;
+    return (int)sort_bits(d_in, d_out, d_tmp, d_out, capacity, 0, 32, nullptr, 0, d_workspace, workspace_len,
+                          (cudaStream_t)stream, &res, reinterpret_cast<KernelTimes *>(times), d_n);
 }
 
 // Peer-mappable device memory for the exchange: plain cudaMalloc (one

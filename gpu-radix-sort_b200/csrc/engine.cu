@@ -68,6 +68,8 @@ using SmemSplit = OnesweepSmem<SORT_THREADS, BALLOT_KPT, true, SplitArg>;
 #define KERNEL_BULK k_onesweep_bulk<SORT_THREADS, SORT_KPT, SORT_MINB, SORT_LB, RANK_ATOMS, RadixBinner, false>
 using SmemBulk = BulkSmem<SORT_THREADS, SORT_KPT, RadixBinner::Arg>;
 #define KERNEL_SPLIT_BULK(NS) k_onesweep_bulk<SORT_THREADS, SPLIT_KPT, SPLIT_BULK_MINB, SORT_LB, RANK_BALLOT, SplitBinner<NS>, true>
+#define KERNEL_SPLIT_BULK_UNORDERED(NS) \
+    k_onesweep_bulk<SORT_THREADS, SPLIT_KPT, SPLIT_BULK_MINB, SORT_LB, RANK_BALLOT, SplitBinner<NS>, true, true>
 using SmemSplitBulk = BulkSmem<SORT_THREADS, SPLIT_KPT, SplitArg>;
 constexpr int kTileSplitBulk = SORT_THREADS * SPLIT_KPT;
 #define KERNEL_B(NBITS) k_onesweep<SORT_THREADS, BALLOT_KPT, BALLOT_MINB, RANK_BALLOT, NBITS, SORT_LB, RadixBinner, false>
@@ -178,35 +180,23 @@ static const int g_hist_mode = env_int("LIBSORT_HIST_MODE", 1);
 static const int g_bulk_out = env_int("LIBSORT_BULK_OUT", 0);
 // the same choice for the splitter scatter of the distributed sort (runs of kilobytes, peer destinations)
 static const int g_bulk_exchange = env_int("LIBSORT_BULK_EXCHANGE", 1);
+// 1 = the planned exchange keeps the tiles of a destination in shard order (look-back), 0 = cursor atomics
+static const int g_exchange_ordered = env_int("LIBSORT_EXCHANGE_ORDERED", 0);
 
 template <int NPASS>
 static cudaError_t launch_hist(const uint32_t *in, size_t n, const PassPlan &plan, uint32_t *ghist, int sms, int occ,
-                               cudaStream_t st)
+                               cudaStream_t st, const uint32_t *dyn_n = nullptr)
 {
     if (g_hist_mode == 1 && n >= (1u << 16)) {
-        auto kern = k_histogram_lanes<NPASS, 1024>;
-        static std::atomic<bool> attr_set{false};
+        auto kern = k_histogram_lanes<NPASS, 1024>;  // shared-memory attribute: set per device in dev_info()
         const int smem = NPASS * RADIX * 32 * (int)sizeof(uint32_t);
-        if (!attr_set.load()) {
-            // set on every device the first time through (attribute is per device)
-            int cur = 0, ndev = 0;
-            cudaGetDevice(&cur);
-            cudaGetDeviceCount(&ndev);
-            for (int d = 0; d < ndev; d++) {
-                cudaSetDevice(d);
-                cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-                if (e != cudaSuccess) { cudaSetDevice(cur); return e; }
-            }
-            cudaSetDevice(cur);
-            attr_set.store(true);
-        }
         const size_t want = (n / 4 + 1024 * 4 - 1) / (1024 * 4);
         const int grid = (int)std::max<size_t>(1, std::min<size_t>((size_t)sms, want));
-        kern<<<grid, 1024, smem, st>>>(in, n, plan, ghist);
+        kern<<<grid, 1024, smem, st>>>(in, n, plan, ghist, dyn_n);
     } else {
         const size_t want = (n / 4 + HIST_THREADS * 4 - 1) / (HIST_THREADS * 4);
         const int grid = (int)std::max<size_t>(1, std::min<size_t>((size_t)sms * occ, want));
-        k_histogram<NPASS, HIST_THREADS, HIST_REPL><<<grid, HIST_THREADS, 0, st>>>(in, n, plan, ghist);
+        k_histogram<NPASS, HIST_THREADS, HIST_REPL><<<grid, HIST_THREADS, 0, st>>>(in, n, plan, ghist, dyn_n);
     }
     return cudaSuccess;
 }
@@ -230,8 +220,15 @@ static cudaError_t choose_rank_mode(int dev, bool *atoms)
     int sms = 1;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     if (err == cudaSuccess) {
-        k_selftest_atoms_order<<<sms, 1024>>>(d_bad, 256);
-        err = cudaMemcpy(h_bad, d_bad, sizeof(h_bad), cudaMemcpyDeviceToHost);
+        cudaStream_t st = nullptr;  // private stream: the legacy default stream would serialise with the caller's work
+        err = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking);
+        if (err == cudaSuccess) {
+            err = cudaMemsetAsync(d_bad, 0, sizeof(h_bad), st);
+            k_selftest_atoms_order<<<sms, 1024, 0, st>>>(d_bad, 256);
+            if (err == cudaSuccess) err = cudaMemcpyAsync(h_bad, d_bad, sizeof(h_bad), cudaMemcpyDeviceToHost, st);
+            if (err == cudaSuccess) err = cudaStreamSynchronize(st);
+            cudaStreamDestroy(st);
+        }
     }
     cudaFree(d_bad);
     if (err != cudaSuccess) return err;
@@ -258,6 +255,8 @@ static cudaError_t dev_info(DevInfo **out)
             {(const void *)KERNEL_BULK, (int)sizeof(SmemBulk)},
             {(const void *)KERNEL_SPLIT_BULK(1), (int)sizeof(SmemSplitBulk)}, {(const void *)KERNEL_SPLIT_BULK(3), (int)sizeof(SmemSplitBulk)},
             {(const void *)KERNEL_SPLIT_BULK(7), (int)sizeof(SmemSplitBulk)}, {(const void *)KERNEL_SPLIT_BULK(15), (int)sizeof(SmemSplitBulk)},
+            {(const void *)KERNEL_SPLIT_BULK_UNORDERED(1), (int)sizeof(SmemSplitBulk)}, {(const void *)KERNEL_SPLIT_BULK_UNORDERED(3), (int)sizeof(SmemSplitBulk)},
+            {(const void *)KERNEL_SPLIT_BULK_UNORDERED(7), (int)sizeof(SmemSplitBulk)}, {(const void *)KERNEL_SPLIT_BULK_UNORDERED(15), (int)sizeof(SmemSplitBulk)},
             {(const void *)KERNEL_B(8), (int)sizeof(SmemB)},     {(const void *)KERNEL_B(0), (int)sizeof(SmemB)},
             {(const void *)KERNEL_SPLIT(1), (int)sizeof(SmemSplit)},  {(const void *)KERNEL_SPLIT(3), (int)sizeof(SmemSplit)},
             {(const void *)KERNEL_SPLIT(7), (int)sizeof(SmemSplit)},  {(const void *)KERNEL_SPLIT(15), (int)sizeof(SmemSplit)},
@@ -265,6 +264,15 @@ static cudaError_t dev_info(DevInfo **out)
         for (auto &k : kernels) {
             e = cudaFuncSetAttribute(k.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, k.smem);
             if (e != cudaSuccess) return e;
+        }
+        {   // K1, bank-private layout: NPASS x 32 KB of dynamic shared memory (this device only)
+            const void *hk[] = {(const void *)k_histogram_lanes<1, 1024>, (const void *)k_histogram_lanes<2, 1024>,
+                                (const void *)k_histogram_lanes<3, 1024>, (const void *)k_histogram_lanes<4, 1024>};
+            for (int np = 1; np <= 4; np++) {
+                e = cudaFuncSetAttribute(hk[np - 1], cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         np * RADIX * 32 * (int)sizeof(uint32_t));
+                if (e != cudaSuccess) return e;
+            }
         }
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.occ_a, KERNEL_A(8), SORT_THREADS, sizeof(SmemA));
         if (e != cudaSuccess) return e;
@@ -384,7 +392,7 @@ static cudaError_t finish_bounds(const uint32_t *sorted, size_t n, uint32_t offs
 
 cudaError_t sort_bits(const uint32_t *in, uint32_t *a, uint32_t *b, uint32_t *want, size_t n, uint32_t offset,
                       uint32_t width, uint32_t *d_bounds, int bounds_mode, void *workspace, size_t workspace_len,
-                      cudaStream_t st, uint32_t **result, KernelTimes *times)
+                      cudaStream_t st, uint32_t **result, KernelTimes *times, const uint32_t *dyn_n)
 {
     if (n > 0xffffffffull) return cudaErrorInvalidValue;
     if (d_bounds && width > 31) return cudaErrorInvalidValue;
@@ -414,7 +422,9 @@ cudaError_t sort_bits(const uint32_t *in, uint32_t *a, uint32_t *b, uint32_t *wa
     CK(dev_info(&dev));
     uint32_t *ws = static_cast<uint32_t *>(workspace);
     uint32_t *ghist = ws + WS_HIST, *base = ws + WS_BASE, *tickets = ws + WS_TICKET, *desc = ws + WS_DESC;
-    const int k3 = (dev->rank_atoms && k3_selected() >= 0 && dev->occ_k3[k3_selected()] > 0) ? k3_selected() : -1;
+    // dyn_n (key count read on the device, n = capacity): plain kernels, one look-back portion, no boundaries
+    if (dyn_n && (d_bounds || n >= (1ull << 30))) return cudaErrorInvalidValue;
+    const int k3 = (!dyn_n && dev->rank_atoms && k3_selected() >= 0 && dev->occ_k3[k3_selected()] > 0) ? k3_selected() : -1;
     const int tile = k3 >= 0 ? g_k3[k3].tile : dev->rank_atoms ? kTileA : kTileB;
     const size_t ntiles = num_tiles(n, tile);
     const uint32_t ptiles = portion_tiles(tile);
@@ -429,17 +439,17 @@ cudaError_t sort_bits(const uint32_t *in, uint32_t *a, uint32_t *b, uint32_t *wa
 
     // K1: one upsweep, all digits
     switch (P) {
-        case 1: CK(launch_hist<1>(in, n, plan, ghist, dev->sms, dev->hist_occ, st)); break;
-        case 2: CK(launch_hist<2>(in, n, plan, ghist, dev->sms, dev->hist_occ, st)); break;
-        case 3: CK(launch_hist<3>(in, n, plan, ghist, dev->sms, dev->hist_occ, st)); break;
-        default: CK(launch_hist<4>(in, n, plan, ghist, dev->sms, dev->hist_occ, st)); break;
+        case 1: CK(launch_hist<1>(in, n, plan, ghist, dev->sms, dev->hist_occ, st, dyn_n)); break;
+        case 2: CK(launch_hist<2>(in, n, plan, ghist, dev->sms, dev->hist_occ, st, dyn_n)); break;
+        case 3: CK(launch_hist<3>(in, n, plan, ghist, dev->sms, dev->hist_occ, st, dyn_n)); break;
+        default: CK(launch_hist<4>(in, n, plan, ghist, dev->sms, dev->hist_occ, st, dyn_n)); break;
     }
     launches++;
     tm.mark();
     const bool bounds_from_hist = d_bounds && P == 1 && plan.mask[0] == ngroups - 1;
     // constant-digit passes become copies (single-portion inputs only: the copy's destination is `dst` itself)
     k_scan_hist<<<P, RADIX, 0, st>>>(ghist, base, bounds_from_hist ? d_bounds : nullptr, (uint32_t)ngroups, (uint32_t)n,
-                                     nportions == 1 ? tickets + SKIP_OFFSET : nullptr);
+                                     nportions == 1 ? tickets + SKIP_OFFSET : nullptr, dyn_n);
     launches++;
     tm.mark();
 
@@ -470,14 +480,14 @@ cudaError_t sort_bits(const uint32_t *in, uint32_t *a, uint32_t *b, uint32_t *wa
                 const int gridk = (int)std::min<size_t>(nt, (size_t)dev->sms * dev->occ_k3[k3]);
                 g_k3[k3].fn<<<gridk, g_k3[k3].threads, g_k3[k3].smem, st>>>(src + k0, dst, (uint32_t)(k1 - k0), barg, bcur, bnext, dsc, tk,
                                                                            nt, use_tma);
-            } else if (dev->rank_atoms && g_bulk_out && dev->occ_bulk > 0) {
+            } else if (!dyn_n && dev->rank_atoms && g_bulk_out && dev->occ_bulk > 0) {
                 const int gridb = (int)std::min<size_t>(nt, (size_t)dev->sms * dev->occ_bulk);
                 KERNEL_BULK<<<gridb, SORT_THREADS, sizeof(SmemBulk), st>>>(src + k0, dst, (uint32_t)(k1 - k0), barg, bcur, bnext, dsc, tk,
                                                                           nt, use_tma);
             } else {
                 auto kern = dev->rank_atoms ? (full_digit ? KERNEL_A(8) : KERNEL_A(0)) : (full_digit ? KERNEL_B(8) : KERNEL_B(0));
                 const size_t smem = dev->rank_atoms ? sizeof(SmemA) : sizeof(SmemB);
-                kern<<<grid, SORT_THREADS, smem, st>>>(src + k0, dst, (uint32_t)(k1 - k0), barg, bcur, bnext, dsc, tk, nt, use_tma);
+                kern<<<grid, SORT_THREADS, smem, st>>>(src + k0, dst, (uint32_t)(k1 - k0), barg, bcur, bnext, dsc, tk, nt, use_tma, dyn_n);
             }
             launches++;
         }
@@ -513,6 +523,34 @@ cudaError_t sort_bits(const uint32_t *in, uint32_t *a, uint32_t *b, uint32_t *wa
         times->boundaries_ms = tm.span(3 + P);
         times->npass = P;
         times->launches = launches;
+    }
+    return cudaSuccess;
+}
+
+// Did any atomic-ranking kernel on the current device see lanes served out of order since the
+// last audit?  Synchronises `st`.  On a violation the device is switched to the ballot kernels for
+// the rest of the process; the caller repeats whatever it sorted since the previous audit.
+cudaError_t rank_audit(cudaStream_t st, bool *violated)
+{
+    *violated = false;
+    DevInfo *dev = nullptr;
+    CK(dev_info(&dev));
+    if (!dev->rank_atoms) return cudaSuccess;
+    unsigned int flag = 0;
+    CK(cudaMemcpyFromSymbolAsync(&flag, g_rank_violation, sizeof(flag), 0, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (flag) {
+        int d = 0;
+        cudaGetDevice(&d);
+        fprintf(stderr, "libsort: device %d served colliding shared atomics out of lane order; switching to ballot ranking\n", d);
+        {
+            std::lock_guard<std::mutex> lk(g_dev_mu);
+            dev->rank_atoms = false;
+        }
+        flag = 0;
+        CK(cudaMemcpyToSymbolAsync(g_rank_violation, &flag, sizeof(flag), 0, cudaMemcpyHostToDevice, st));
+        CK(cudaStreamSynchronize(st));
+        *violated = true;
     }
     return cudaSuccess;
 }
@@ -579,7 +617,48 @@ cudaError_t scatter_by_splitters(const uint32_t *in, size_t n, const uint32_t *s
     } else {
         auto kern = nsplit <= 1 ? KERNEL_SPLIT(1) : nsplit <= 3 ? KERNEL_SPLIT(3) : nsplit <= 7 ? KERNEL_SPLIT(7) : KERNEL_SPLIT(15);
         kern<<<grid, SORT_THREADS, sizeof(SmemSplit), st>>>(in, nullptr, (uint32_t)n, arg, d_ptrs, nullptr, ws + WS_DESC,
-                                                            ws + WS_TICKET, (uint32_t)ntiles, use_tma);
+                                                            ws + WS_TICKET, (uint32_t)ntiles, use_tma, nullptr);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t exchange_planned(const uint32_t *in, size_t n, const uint32_t *splitters, int nranks, int me,
+                             const uint32_t *d_count_matrix, const unsigned long long *d_peer_bases, size_t cap,
+                             uint32_t *d_nrecv, uint32_t *d_status, void *workspace, size_t workspace_len, cudaStream_t st)
+{
+    if (nranks < 1 || nranks > MAX_SPLITTERS + 1 || me < 0 || me >= nranks || n >= (1ull << 30)) return cudaErrorInvalidValue;
+    if (workspace_len < workspace_bytes(n) || !workspace) return cudaErrorInvalidValue;
+    DevInfo *dev = nullptr;
+    CK(dev_info(&dev));
+    uint32_t *ws = static_cast<uint32_t *>(workspace);
+    const bool bulk = g_bulk_exchange && dev->occ_split_bulk > 0;
+    const size_t ntiles = num_tiles(n, bulk ? kTileSplitBulk : kTileB);
+    CK(cudaMemsetAsync(ws, 0, (WS_DESC + ntiles * RADIX) * sizeof(uint32_t), st));
+    unsigned long long *d_ptrs = reinterpret_cast<unsigned long long *>(ws + WS_HIST);
+    k_plan_exchange<<<1, 32, 0, st>>>(d_count_matrix, nranks, me, d_peer_bases, (unsigned long long)cap, d_ptrs, d_nrecv,
+                                      d_status, ws + WS_TICKET);
+    if (n == 0) return cudaGetLastError();
+    const int nsplit = nranks - 1;
+    const int use_tma = (reinterpret_cast<uintptr_t>(in) & 15u) == 0;
+    const SplitArg arg{splitters, nsplit};
+    if (bulk) {
+        // a full local sort follows the exchange: the tiles need not arrive in order (one cursor
+        // atomic per destination instead of the look-back); LIBSORT_EXCHANGE_ORDERED=1 keeps the chain
+        auto kern = g_exchange_ordered
+                        ? (nsplit <= 1 ? KERNEL_SPLIT_BULK(1) : nsplit <= 3 ? KERNEL_SPLIT_BULK(3) : nsplit <= 7 ? KERNEL_SPLIT_BULK(7)
+                                                                                                                 : KERNEL_SPLIT_BULK(15))
+                        : (nsplit <= 1   ? KERNEL_SPLIT_BULK_UNORDERED(1)
+                           : nsplit <= 3 ? KERNEL_SPLIT_BULK_UNORDERED(3)
+                           : nsplit <= 7 ? KERNEL_SPLIT_BULK_UNORDERED(7)
+                                         : KERNEL_SPLIT_BULK_UNORDERED(15));
+        const int gridb = (int)std::min<size_t>(ntiles, (size_t)dev->sms * dev->occ_split_bulk);
+        kern<<<gridb, SORT_THREADS, sizeof(SmemSplitBulk), st>>>(in, nullptr, (uint32_t)n, arg, d_ptrs, nullptr, ws + WS_DESC,
+                                                                 ws + WS_TICKET, (uint32_t)ntiles, use_tma);
+    } else {
+        auto kern = nsplit <= 1 ? KERNEL_SPLIT(1) : nsplit <= 3 ? KERNEL_SPLIT(3) : nsplit <= 7 ? KERNEL_SPLIT(7) : KERNEL_SPLIT(15);
+        const int grid = (int)std::min<size_t>(ntiles, (size_t)dev->sms * dev->occ_split);
+        kern<<<grid, SORT_THREADS, sizeof(SmemSplit), st>>>(in, nullptr, (uint32_t)n, arg, d_ptrs, nullptr, ws + WS_DESC,
+                                                            ws + WS_TICKET, (uint32_t)ntiles, use_tma, nullptr);
     }
     return cudaGetLastError();
 }
@@ -647,11 +726,11 @@ cudaError_t step_scatter(const uint32_t *in, size_t n, uint32_t shift, uint32_t 
     if (dev->rank_atoms) {
         const int grid = (int)std::min<size_t>(ntiles, (size_t)dev->sms * dev->occ_sliced_a);
         KERNEL_SLICED_A<<<grid, SORT_THREADS, sizeof(SmemSlicedA), st>>>(in, nullptr, (uint32_t)n, arg, d_table, nullptr,
-                                                                         ws + WS_DESC, ws + WS_TICKET, (uint32_t)ntiles, use_tma);
+                                                                         ws + WS_DESC, ws + WS_TICKET, (uint32_t)ntiles, use_tma, nullptr);
     } else {
         const int grid = (int)std::min<size_t>(ntiles, (size_t)dev->sms * dev->occ_sliced_b);
         KERNEL_SLICED_B<<<grid, SORT_THREADS, sizeof(SmemSlicedB), st>>>(in, nullptr, (uint32_t)n, arg, d_table, nullptr,
-                                                                         ws + WS_DESC, ws + WS_TICKET, (uint32_t)ntiles, use_tma);
+                                                                         ws + WS_DESC, ws + WS_TICKET, (uint32_t)ntiles, use_tma, nullptr);
     }
     return cudaGetLastError();
 }

@@ -22,6 +22,10 @@ struct KernelTimes {        // milliseconds, filled when requested
     int launches;           // kernels launched by this call
 };
 
+// Audit of the atomic-ranking assumption: true if a kernel on the current device
+// flagged an out-of-order rank since the last audit; the device then falls back to ballot ranking.
+cudaError_t rank_audit(cudaStream_t stream, bool *violated);
+
 // Keys per scatter tile of the compiled-in kernel variant.
 int tile_keys();
 
@@ -37,10 +41,13 @@ size_t workspace_bytes(size_t n);
 // non-null the result is forced into `want` (one extra device copy when the
 // pass parity does not land there).  d_bounds (nullable, 1<<width entries)
 // receives the group boundaries.  All work is enqueued on `stream`; nothing
-// synchronises unless `times` is non-null.
+// synchronises unless `times` is non-null.  dyn_n (nullable, DEVICE word): the key count is read on
+// the device when the kernels run, `n` is then only the capacity the launches and the look-back
+// descriptors are sized for (n < 2^30, no boundaries) -- the distributed sort's local sort, whose
+// input size is known to the GPU (count matrix) before it is known to the host.
 cudaError_t sort_bits(const uint32_t *in, uint32_t *a, uint32_t *b, uint32_t *want, size_t n, uint32_t offset,
                       uint32_t width, uint32_t *d_bounds, int bounds_mode, void *workspace, size_t workspace_len,
-                      cudaStream_t stream, uint32_t **result, KernelTimes *times);
+                      cudaStream_t stream, uint32_t **result, KernelTimes *times, const uint32_t *dyn_n = nullptr);
 
 // Distributed-sort building blocks (one rank per GPU).
 // sample_keys: nsamples stratified pseudo-random keys of the shard.
@@ -77,6 +84,16 @@ cudaError_t step_counts(const uint32_t *in, size_t n, uint32_t shift, uint32_t n
 cudaError_t step_bases(const uint32_t *d_gathered, int nranks, int me, void *d_table, cudaStream_t st);
 cudaError_t step_scatter(const uint32_t *in, size_t n, uint32_t shift, uint32_t nbits, const void *d_table,
                          void *workspace, size_t workspace_len, cudaStream_t st);
+
+// The exchange with its receive layout planned on the device: d_count_matrix = the all-gathered
+// nranks x 16 per-destination counts (split_counts of every rank), d_peer_bases[r] = rank r's
+// receive buffer as mapped here (DEVICE array), cap = keys a receive buffer holds.  Writes
+// *d_nrecv (keys arriving at this rank; 0 on overflow) and raises *d_status on overflow (then no
+// key is stored anywhere).  No host synchronisation.
+cudaError_t exchange_planned(const uint32_t *in, size_t n, const uint32_t *splitters, int nranks, int me,
+                             const uint32_t *d_count_matrix, const unsigned long long *d_peer_bases, size_t cap,
+                             uint32_t *d_nrecv, uint32_t *d_status, void *workspace, size_t workspace_len,
+                             cudaStream_t st);
 
 // Test hook: cap the number of tiles per look-back portion (0 = default,
 // i.e. the largest portion whose key count fits the 30-bit descriptors).

@@ -5,9 +5,14 @@
 //       k_scan_hist      256-bin exclusive scans -> global bucket bases
 //                        (and, for width <= 8, the exact boundaries).
 //   K3  k_onesweep       one stable digit-scatter pass (8 B/key): 1-D bulk TMA
-//                        stages each key tile in shared memory (double
-//                        buffered, persistent CTAs, dynamic tile tickets),
-//                        __match_any_sync ranks keys, keys are re-ordered in
+//                        stages each key tile in shared memory (ONE tile buffer,
+//                        persistent CTAs, late dynamic tile tickets; the next
+//                        tile's load runs under this tile's stores).  Keys are
+//                        ranked with returning shared-memory atomics (default,
+//                        self-tested and audited per tile) or with one ballot per
+//                        digit bit (RANK_BALLOT) -- MATCH.ANY measured 62 cycles
+//                        per warp-op on B200 (profiles/r01_microbench_primitives.log)
+//                        and is only used for <= 2-bit digits -- re-ordered in
 //                        shared memory and written coalesced per bucket.
 //   K2  (inside K3)      chained scan with decoupled look-back over per-tile
 //                        bucket counts; replaces the reference's multi-kernel
@@ -46,9 +51,10 @@ __device__ __forceinline__ uint32_t digit_of(uint32_t key, uint32_t shift, uint3
 // to thin out same-address atomic collisions.  Flushed once per CTA.
 template <int NPASS, int THREADS, int REPL>
 __global__ void __launch_bounds__(THREADS) k_histogram(const uint32_t *__restrict__ in, size_t n, PassPlan plan,
-                                                      uint32_t *__restrict__ ghist)
+                                                      uint32_t *__restrict__ ghist, const uint32_t *__restrict__ dyn_n)
 {
     __shared__ uint32_t s_hist[REPL][NPASS][RADIX];
+    if (dyn_n) n = *dyn_n;  // key count decided on the device (the launch was sized for the capacity)
     for (int i = threadIdx.x; i < REPL * NPASS * RADIX; i += THREADS) (&s_hist[0][0][0])[i] = 0;
     __syncthreads();
 
@@ -102,9 +108,10 @@ __global__ void __launch_bounds__(THREADS) k_histogram(const uint32_t *__restric
 // NPASS * 32 KB of dynamic shared memory, one CTA per SM.
 template <int NPASS, int THREADS>
 __global__ void __launch_bounds__(THREADS, 1) k_histogram_lanes(const uint32_t *__restrict__ in, size_t n, PassPlan plan,
-                                                               uint32_t *__restrict__ ghist)
+                                                               uint32_t *__restrict__ ghist, const uint32_t *__restrict__ dyn_n)
 {
     extern __shared__ __align__(16) uint32_t s_lane_hist[];  // [NPASS][RADIX][32]
+    if (dyn_n) n = *dyn_n;
     for (int i = threadIdx.x; i < NPASS * RADIX * 32; i += THREADS) s_lane_hist[i] = 0;
     __syncthreads();
     const uint32_t lane = threadIdx.x & 31;
@@ -180,9 +187,10 @@ constexpr int SKIP_STRIDE = 8;   // one flag per (pass, portion) slot, beside th
 constexpr int SKIP_OFFSET = 32;  // flag of a pass = its ticket word + SKIP_OFFSET
 __global__ void __launch_bounds__(256) k_scan_hist(const uint32_t *__restrict__ ghist, uint32_t *__restrict__ base,
                                                   uint32_t *__restrict__ d_exact, uint32_t ngroups, uint32_t n,
-                                                  uint32_t *__restrict__ skip)
+                                                  uint32_t *__restrict__ skip, const uint32_t *__restrict__ dyn_n)
 {
     __shared__ uint32_t s_warp[8];
+    if (dyn_n) n = *dyn_n;
     const int p = blockIdx.x;
     uint32_t c = ghist[p * RADIX + threadIdx.x];
     uint32_t ex = block_excl_scan_256(c, s_warp, nullptr);
@@ -435,6 +443,10 @@ struct OnesweepSmem {
     uint32_t nslice;
 };
 
+// Raised by the atomic-ranking kernels when the per-tile audit sees colliding lanes served out of
+// lane order (never observed on sm_100; see DESIGN.md "atomic ranking").  One word per device.
+static __device__ unsigned int g_rank_violation = 0;
+
 constexpr int RANK_BALLOT = 0;  // one vote.ballot per digit bit + a leader atomic: architecturally ordered
 constexpr int RANK_ATOMS = 1;   // rank = return value of the warp's shared atomic (see DESIGN.md "atomic ranking")
 
@@ -454,9 +466,13 @@ template <int THREADS, int KPT, int MINB, int RANK, int NBITS, int LB, class Bin
 __global__ void __launch_bounds__(THREADS, MINB)
     k_onesweep(const uint32_t *__restrict__ in, uint32_t *__restrict__ out, uint32_t n, const typename Binner::Arg binner_arg,
                const void *__restrict__ base_v, uint32_t *__restrict__ base_next, uint32_t *__restrict__ desc,
-               uint32_t *__restrict__ ticket, uint32_t ntiles, int use_tma)
+               uint32_t *__restrict__ ticket, uint32_t ntiles, int use_tma, const uint32_t *__restrict__ dyn_n)
 {
     using Smem = OnesweepSmem<THREADS, KPT, PTR_OUT, typename Binner::Arg>;
+    if (dyn_n) {  // key count decided on the device: the grid and the descriptors were sized for the capacity
+        n = *dyn_n;
+        ntiles = (n + (uint32_t)(THREADS * KPT) - 1u) / (uint32_t)(THREADS * KPT);
+    }
     static_assert(!(RANK == RANK_ATOMS && Binner::kByPosition), "the heavy-tile path bins by key alone");
     constexpr int TILE = Smem::TILE;
     constexpr int NWARPS = Smem::NWARPS;
@@ -592,6 +608,16 @@ __global__ void __launch_bounds__(THREADS, MINB)
                     const uint32_t p4 =
                         atomicAdd(reinterpret_cast<uint32_t *>(my_hist + binner.bin4(key[i], tile_base + wbase + i * 32)), 4u);
                     *reinterpret_cast<uint32_t *>(tile_bytes + p4) = key[i];
+                    if (i == 0) {
+                        // audit of the lane-order assumption on one row of every tile (1/KPT of the
+                        // keys): lanes of this instruction with the same digit must have been served
+                        // in ascending lane order.  A violation raises g_rank_violation; the host side
+                        // then repeats the call with the ballot kernels (engine.cu rank_audit).
+                        const uint32_t d4 = binner.bin4(key[0], tile_base + wbase);
+                        const uint32_t peers = match_digit<NBITS>(d4 >> 2, binner.nbits());
+                        const uint32_t first = __shfl_sync(0xffffffffu, p4, __ffs(peers) - 1);
+                        if (p4 != first + 4u * __popc(peers & lanemask_lt())) atomicOr(&g_rank_violation, 1u);
+                    }
                 }
             } else {
                 // one digit dominates the tile (skewed input): out-of-line path, see rank_tile_heavy
@@ -853,6 +879,36 @@ __global__ void __launch_bounds__(RADIX) k_step_bases(const uint32_t *__restrict
 __global__ void k_store_ptrs(const PtrTable t, unsigned long long *__restrict__ dst)
 {
     if (threadIdx.x <= MAX_SPLITTERS) dst[threadIdx.x] = t.p[threadIdx.x];
+}
+
+// Receive layout of the exchange, computed where the count matrix already is (no host round
+// trip): cm[s][d] = keys rank s sends to rank d (nranks x 16 words, all-gathered).  Rank `me`
+// writes its keys for rank d behind those of the ranks before it: dest_ptrs[d] = peer_base[d] +
+// 4 * sum over s < me of cm[s][d]; what arrives here is nrecv = sum over s of cm[s][me].  If any
+// rank would receive more than `cap` keys, status is raised and the scatter that follows is
+// switched off (its tile ticket starts past the last tile) -- every rank sees the same matrix and
+// takes the same decision.
+__global__ void k_plan_exchange(const uint32_t *__restrict__ cm, int nranks, int me,
+                                const unsigned long long *__restrict__ peer_base, unsigned long long cap,
+                                unsigned long long *__restrict__ dest_ptrs, uint32_t *__restrict__ nrecv,
+                                uint32_t *__restrict__ status, uint32_t *__restrict__ ticket)
+{
+    const int d = threadIdx.x;
+    unsigned long long off = 0, tot = 0;
+    if (d < nranks) {
+        for (int s = 0; s < nranks; s++) {
+            const uint32_t c = cm[s * (MAX_SPLITTERS + 1) + d];
+            if (s < me) off += c;
+            tot += c;
+        }
+    }
+    const bool any_over = __any_sync(0xffffffffu, d < nranks && tot > cap);
+    if (d < nranks) dest_ptrs[d] = peer_base[d] + 4ull * off;
+    if (d == me) *nrecv = any_over ? 0u : (uint32_t)tot;
+    if (d == 0 && any_over) {
+        *status = 1u;
+        *ticket = 0x7fffffffu;
+    }
 }
 
 // ------------------------------------------------------------ boundaries --

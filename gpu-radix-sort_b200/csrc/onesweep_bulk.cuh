@@ -44,7 +44,11 @@ struct BulkSmem {
 // destination address per bin (local or NVLink-mapped peer memory) -- the splitter
 // scatter of the distributed sort, where a tile has at most 16 long runs and the
 // bulk-copy engine, not the SM's store path, rides out the NVLink latency.
-template <int THREADS, int KPT, int MINB, int LB, int RANK, class Binner, bool PTR_OUT>
+// UNORDERED (PTR_OUT only): the tiles of this launch may land in any order inside a destination's
+// range -- the distributed sort sorts what arrived anyway -- so a tile reserves its place with ONE
+// atomicAdd per destination on a cursor array (`desc`, 16 zeroed words) instead of waiting, fully
+// exposed here, for the look-back over all earlier tiles.
+template <int THREADS, int KPT, int MINB, int LB, int RANK, class Binner, bool PTR_OUT, bool UNORDERED = false>
 __global__ void __launch_bounds__(THREADS, MINB)
     k_onesweep_bulk(const uint32_t *__restrict__ in, uint32_t *__restrict__ out, uint32_t n, const typename Binner::Arg binner_arg,
                     const void *__restrict__ base_v, uint32_t *__restrict__ base_next, uint32_t *__restrict__ desc,
@@ -141,10 +145,12 @@ __global__ void __launch_bounds__(THREADS, MINB)
             for (int w = 0; w < NWARPS; w++) padded += s.warp_hist[w][tid];
             my_count = padded;
             if ((uint32_t)tid == pad_bin) my_count -= (uint32_t)TILE - valid;  // padding keys carry the top digit
-            st_relaxed(&desc[(size_t)cur * RADIX + tid], (cur == 0 ? DESC_INCL : DESC_AGG) | my_count);
-
             uint32_t excl = 0;
-            if (cur != 0) {
+            if (UNORDERED) {
+                if (my_count) excl = atomicAdd(&desc[tid], my_count);
+            } else
+                st_relaxed(&desc[(size_t)cur * RADIX + tid], (cur == 0 ? DESC_INCL : DESC_AGG) | my_count);
+            if (!UNORDERED && cur != 0) {
                 // windowed decoupled look-back: LB descriptors per round trip
                 uint32_t j = cur - 1;
                 bool done = false;

@@ -9,11 +9,14 @@ single exchange:
   2. count keys per destination (k_dest_hist), all-gather the P x P count
      matrix (NCCL) -> receive layout
   3. exchange, one of
-       p2p : ONE kernel partitions the shard and stores every key straight into
-             its destination GPU's receive buffer through cudaIpc/NVLink-mapped
-             pointers (k_onesweep<SplitBinner, PTR_OUT>) -- partition + all-to-all fused
-       nccl: partition locally with the same kernel, then NCCL all_to_all_single
-  4. local LSD sort of what arrived (libsortDeviceSort, 4 passes)
+       p2p : the receive layout is derived ON THE DEVICE from the gathered matrix
+             (k_plan_exchange), then ONE kernel partitions the shard and stores every
+             key straight into its destination GPU's receive buffer through
+             cudaIpc/NVLink-mapped pointers (k_onesweep_bulk<SplitBinner, PTR_OUT>) --
+             partition + all-to-all fused, no host round trip anywhere in the sort
+       nccl: host-planned: partition locally with the same kernel, then NCCL all_to_all_single
+  4. local LSD sort of what arrived (4 passes); p2p: libsortDeviceSortDyn, the number of
+     keys that arrived is read by the kernels from device memory
 
 sort_stepwise() is the reference's OWN distributed algorithm on the same plumbing (SURVEY.md 8(f)
 N2): one global counting sort per 8-bit digit, 32/8 exchanges, every key stored straight into the
@@ -37,7 +40,7 @@ import torch.distributed as dist
 from . import binding, distrib_plan
 from .binding import KernelTimes
 
-SAMPLES_PER_RANK = 1 << 15
+SAMPLES_PER_RANK = 1 << 13   # 8 K per rank: the quantiles of P x 8 K samples balance to about 1 %
 
 
 def _u32_to_i32(v64):
@@ -126,10 +129,14 @@ class DistributedSorter:
         self.count_matrix = torch.zeros(16 * self.world, dtype=i32, device=dev)
         self.token = torch.zeros(1, dtype=i32, device=dev)
         self.h_counts = torch.empty(16 * self.world, dtype=i32).pin_memory()
+        self.d_peer_bases = torch.tensor(self.peer_ptrs, dtype=torch.int64, device=dev)
+        self.d_nrecv = torch.zeros(1, dtype=i32, device=dev)
+        self.d_status = torch.zeros(1, dtype=i32, device=dev)
         self.seed = 1
         self._step = None      # lazily built state of sort_stepwise()
         # kernels per sort: sample, sample sort (hist, scan, 4 passes), pick, dest hist, store ptrs,
         # scatter, local sort (hist, scan, 4 passes)
+        # p2p: sample, sample sort (hist, scan, 4 passes), pick, dest hist, plan, scatter, local sort (hist, scan, 4 passes)
         self.launches_per_sort = 1 + 6 + 1 + 1 + 1 + 1 + 6
         self.launches_per_stepwise_sort = 4 * 3    # per step: histogram, bases, scatter
         self.last_totals = None
@@ -152,8 +159,9 @@ class DistributedSorter:
     def _stream(self):
         return torch.cuda.current_stream(self.dev).cuda_stream
 
-    def _plan(self, keys, ev=None):
-        """Steps 1-2: splitters on the device, count matrix on the host (the one host sync)."""
+    def _plan(self, keys, ev=None, on_host=True):
+        """Steps 1-2: splitters and the gathered count matrix on the device; on_host: also read the
+        matrix back (one host sync -- only the NCCL all-to-all mode needs it)."""
         L, st, n, W = self.lib, self._stream(), keys.numel(), self.world
         S = SAMPLES_PER_RANK
         self.seed += 1
@@ -175,12 +183,61 @@ class DistributedSorter:
             dist.all_gather_into_tensor(self.count_matrix, self.counts, group=self.group)
         else:
             self.count_matrix.copy_(self.counts)
+        if not on_host:
+            if ev:
+                ev("counts")
+            return None
         self.h_counts.copy_(self.count_matrix, non_blocking=True)
         torch.cuda.current_stream(self.dev).synchronize()
         cm = self.h_counts.numpy().reshape(W, 16)[:, :W].astype(np.int64)
         if ev:
             ev("counts")
         return cm
+
+    def sort_async(self, keys, ev=None, times=None):
+        """The p2p sort with nothing read back: returns (buffer holding this rank's range, DEVICE tensor
+        with its length).  Everything -- receive layout, exchange, local sort on a device-side key
+        count -- is enqueued on the current stream; the host never waits."""
+        if self.mode != "p2p":
+            raise ValueError("sort_async needs the p2p exchange")
+        if keys.dtype not in (torch.int32, torch.uint32) or not keys.is_cuda or not keys.is_contiguous():
+            raise ValueError("keys must be a contiguous CUDA int32/uint32 tensor")
+        L, st, n, W, me = self.lib, self._stream(), keys.numel(), self.world, self.rank
+        if n > self.n_max:
+            raise ValueError("shard larger than the sorter was built for")
+        self._plan(keys, ev, on_host=False)
+        binding.check(L.libsortDeviceExchangePlanned(keys.data_ptr(), n, self.splitters.data_ptr(), W, me,
+                                                     self.count_matrix.data_ptr(), self.d_peer_bases.data_ptr(), self.cap,
+                                                     self.d_nrecv.data_ptr(), self.d_status.data_ptr(),
+                                                     self.ws.data_ptr(), self.ws.numel(), st), "planned exchange")
+        if W > 1:
+            # stream-ordered barrier: nobody starts sorting before every rank's stores have landed
+            dist.all_reduce(self.token, group=self.group)
+        if ev:
+            ev("exchange")
+        binding.check(L.libsortDeviceSortDyn(self.recv_ptr, self.out.data_ptr(), self.tmp.data_ptr(), self.cap,
+                                             self.d_nrecv.data_ptr(), self.ws.data_ptr(), self.ws.numel(), st,
+                                             ctypes.byref(times) if times is not None else None), "local sort")
+        if W > 1:
+            # the receive buffer is overwritten by the next sort's remote stores: fence it
+            dist.all_reduce(self.token, group=self.group)
+        if ev:
+            ev("local_sort")
+        return self.out, self.d_nrecv
+
+    def _finish(self):
+        """Read back what sort_async left on the device: this rank's key count, the per-rank totals
+        and the overflow flag (one synchronisation, after everything has been enqueued)."""
+        W = self.world
+        self.h_counts.copy_(self.count_matrix, non_blocking=True)
+        nrecv, status = int(self.d_nrecv.item()), int(self.d_status.item())
+        cm = self.h_counts.numpy().reshape(W, 16)[:, :W].astype(np.int64)
+        self.last_totals = cm.sum(axis=0)
+        if status:
+            self.d_status.zero_()
+            raise RuntimeError("receive buffer too small: %d keys arrive, capacity %d (raise slack)"
+                               % (int(self.last_totals.max()), self.cap))
+        return nrecv
 
     def sort(self, keys, ev=None, times=None):
         """Sort the union of all ranks' `keys`; returns (tensor view of this rank's range, its length)."""
@@ -189,6 +246,10 @@ class DistributedSorter:
         L, st, n, W, me = self.lib, self._stream(), keys.numel(), self.world, self.rank
         if n > self.n_max:
             raise ValueError("shard larger than the sorter was built for")
+        if self.mode == "p2p":
+            out, _ = self.sort_async(keys, ev=ev, times=times)
+            nrecv = self._finish()
+            return out[:nrecv], nrecv
         cm = self._plan(keys, ev)
         offsets, totals = distrib_plan.recv_layout(cm)
         self.last_totals = totals

@@ -88,6 +88,26 @@ LIBSORT_API int libsortDeviceSplitCounts(const uint32_t *d_in, size_t n, const u
 LIBSORT_API int libsortDeviceScatterToPeers(const uint32_t *d_in, size_t n, const uint32_t *splitters, int nsplit,
                                             const unsigned long long *dest_ptrs, void *d_workspace,
                                             size_t workspace_bytes, void *stream);
+/*
+ * The same exchange and local sort without any host round trip (what DistributedSorter.sort uses):
+ * libsortDeviceExchangePlanned: d_count_matrix = the all-gathered nranks x 16 counts of
+ *     libsortDeviceSplitCounts (DEVICE), d_peer_bases[r] = rank r's receive buffer as mapped on this
+ *     GPU (DEVICE array of nranks addresses), cap = keys a receive buffer holds.  A one-warp kernel
+ *     derives where this rank's keys for every destination go and *d_nrecv (keys arriving here),
+ *     then the fused partition + exchange kernel runs.  If some rank would receive more than cap
+ *     keys, *d_status becomes 1 (sticky; zero it beforehand), *d_nrecv 0 and nothing is stored.
+ * libsortDeviceSortDyn: full 32-bit sort of d_in[0..*d_n) into d_out, the key count read ON THE
+ *     DEVICE when the kernels run; launches, workspace and d_tmp are sized for `capacity` (< 2^30);
+ *     times as for libsortDeviceSort (non-NULL synchronises the stream).
+ */
+LIBSORT_API int libsortDeviceExchangePlanned(const uint32_t *d_in, size_t n, const uint32_t *splitters, int nranks,
+                                             int me, const uint32_t *d_count_matrix,
+                                             const unsigned long long *d_peer_bases, size_t cap, uint32_t *d_nrecv,
+                                             uint32_t *d_status, void *d_workspace, size_t workspace_bytes,
+                                             void *stream);
+LIBSORT_API int libsortDeviceSortDyn(const uint32_t *d_in, uint32_t *d_out, uint32_t *d_tmp, size_t capacity,
+                                     const uint32_t *d_n, void *d_workspace, size_t workspace_bytes, void *stream,
+                                     LibsortKernelTimes *times);
 LIBSORT_API int libsortIpcAlloc(size_t bytes, void **ptr);
 LIBSORT_API int libsortIpcFree(void *ptr);
 LIBSORT_API int libsortIpcExport(void *ptr, void *handle64);
@@ -139,6 +159,18 @@ LIBSORT_API int libsortStepScatter(const uint32_t *d_in, size_t n, uint32_t shif
 /* populateInput at an explicit stream position: arr[i] = element first+i of the
  * fresh-process PCG sequence (reference libsort/utils.cu:63-79).  Thread safe. */
 LIBSORT_API void libsortPopulateInputAt(uint32_t *arr, size_t nelem, uint64_t first);
+
+/*
+ * Audit of the default ranking mode.  The scatter pass ranks keys with returning shared-memory
+ * atomics, which is stable only while the hardware serves colliding lanes of one instruction in
+ * ascending lane order (true on sm_100, self-tested per device, not an architectural promise).
+ * Every tile therefore re-checks one of its rows with ballots; a mismatch raises a device flag.
+ * libsortRankAudit synchronises `stream` and returns 0 = no violation since the last audit,
+ * 1 = violation seen: the device has been switched to the ballot kernels and everything sorted
+ * on it since the last audit must be sorted again; < 0 = CUDA error.  The host-pointer entry
+ * points (gpuPartial, providedGpu) audit and repeat by themselves.
+ */
+LIBSORT_API int libsortRankAudit(void *stream);
 
 /* Number of GPUs in the pool (0 before initLibSort). */
 LIBSORT_API int libsortDeviceCount(void);
