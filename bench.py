@@ -174,6 +174,196 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def _u(t):
+    """uint32 view of an int32 CUDA tensor as int64 values (torch has no unsigned compare)."""
+    return t.to(__import__("torch").int64) & 0xFFFFFFFF
+
+
+def check_partial_on_device(torch, d_in, d_out, bounds, offset, width):
+    """Size-independent checks of a partial sort at full size, on the device: groups ascend,
+    boundaries are the exclusive prefix sums of the group histogram (localTest/tests.cpp:44-68),
+    the multiset is preserved.  (Stability has its own leg: stability_leg.)"""
+    n = d_out.numel()
+    mask = (1 << width) - 1
+    g_out = (_u(d_out) >> offset) & mask
+    ok_groups = bool((g_out[1:] >= g_out[:-1]).all())
+    del g_out
+    g_in = ((_u(d_in) >> offset) & mask)
+    hist = torch.bincount(g_in, minlength=1 << width)
+    del g_in
+    excl = torch.cumsum(hist, 0) - hist
+    ok_bounds = bool((excl == _u(bounds)).all())
+    a, b = _u(d_in), _u(d_out)
+    ok_multiset = int(a.sum()) == int(b.sum()) and int((a * a % 1000003).sum()) == int((b * b % 1000003).sum())
+    return {"groups_ascending": ok_groups, "boundaries_are_prefix_sums": ok_bounds, "multiset_preserved": ok_multiset,
+            "keys": n}
+
+
+def stability_leg(torch, dev, binding, width, n):
+    """Full-size stability check of the default ranking path: keys (i << width) | h(i), partial sort
+    on (0, width) -- inside every bucket the keys must still ascend, i.e. keep their input order
+    (reference contract: stable LSD passes, libsort/sort.cu:322-346)."""
+    i = torch.arange(n, dtype=torch.int64, device="cuda")
+    h = (i * 2654435761 >> 7) & ((1 << width) - 1)
+    keys64 = ((i << width) | h) & 0xFFFFFFFF
+    keys = torch.where(keys64 >= (1 << 31), keys64 - (1 << 32), keys64).to(torch.int32)
+    del i, h, keys64
+    out = dev.sort_bits(keys, 0, width, boundary_mode=binding.BOUNDS_EXACT)
+    o = _u(out)
+    g = o & ((1 << width) - 1)
+    same = g[1:] == g[:-1]
+    ok = bool(((o[1:] > o[:-1]) | ~same).all()) and bool((g[1:] >= g[:-1]).all())
+    return {"width": width, "keys": n, "stable": ok}
+
+
+def single_gpu_extras(args, torch, np, pkg, dev, binding, h_keys, peak):
+    """Everything BASELINE.json names besides the headline config, measured in the same run
+    (extras never touch the headline keys; a failing extra is reported, not fatal)."""
+    import ctypes
+    lib = pkg.lib()
+    ex = {}
+
+    def timed(fn, reps=5, warm=2):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    # c1: localTest ./radix_sort -- 1M keys, GPU full sort == CPU sort (BASELINE configs[0])
+    try:
+        n1 = 1 << 20
+        k1 = torch.from_numpy(h_keys[:n1].view(np.int32)).cuda()
+        o1, t1 = torch.empty_like(k1), torch.empty_like(k1)
+        ms1 = timed(lambda: dev.sort(k1, out=o1, tmp=t1), reps=20)
+        want = np.sort(h_keys[:n1])
+        ex["c1_localtest_1M"] = {"keys": n1, "ms": ms1, "gkeys_s": n1 / ms1 / 1e6,
+                                 "equals_cpu_sort": bool(np.array_equal(o1.cpu().numpy().view(np.uint32), want))}
+    except Exception as e:  # noqa: BLE001
+        ex["c1_localtest_1M"] = {"error": repr(e)}
+
+    # c3: partial sorts of 2^29 keys with boundaries (BASELINE configs[2]; analysis/libsort8b,16b.csv)
+    try:
+        n3 = 1 << 29
+        h3 = np.empty(n3, dtype=np.uint32)
+        lib.libsortPopulateInputAt(h3.ctypes.data, n3, 0)
+        k3 = torch.from_numpy(h3.view(np.int32)).cuda()
+        del h3
+        o3, t3 = torch.empty_like(k3), torch.empty_like(k3)
+        rows = []
+        for off, w in ((0, 8), (0, 16), (24, 8), (16, 16)):
+            kt = binding.KernelTimes()
+            _, bnd = dev.sort_bits(k3, off, w, out=o3, tmp=t3, boundaries=True, boundary_mode=binding.BOUNDS_EXACT, times=kt)
+            ms3 = timed(lambda: dev.sort_bits(k3, off, w, out=o3, tmp=t3, boundaries=True, boundary_mode=binding.BOUNDS_EXACT),
+                        reps=5, warm=1)
+            passes = [kt.pass_ms[i] for i in range(kt.npass)]
+            nb = 4 + 8 * len(passes)
+            row = {"offset": off, "width": w, "keys": n3, "ms": ms3, "gkeys_s": n3 / ms3 / 1e6,
+                   "algorithmic_bytes_per_key": nb, "gbs": nb * n3 / ms3 / 1e6, "frac_of_peak": nb * n3 / ms3 / 1e6 / peak,
+                   "pass_ms": passes, "pass_frac_of_peak": [8.0 * n3 / (p * 1e-3) / 1e9 / peak for p in passes],
+                   "histogram_ms": kt.histogram_ms}
+            row.update(check_partial_on_device(torch, k3, o3, bnd, off, w))
+            rows.append(row)
+        ex["c3_partial_512M"] = rows
+        del k3, o3, t3
+    except Exception as e:  # noqa: BLE001
+        ex["c3_partial_512M"] = {"error": repr(e)}
+    torch.cuda.empty_cache()
+
+    # stability of the default (atomic-ranking) path at full size, and the per-tile audit flag
+    try:
+        ex["stability"] = [stability_leg(torch, dev, binding, 4, 1 << 28), stability_leg(torch, dev, binding, 8, 1 << 24)]
+        ex["rank_audit_violations"] = int(lib.libsortRankAudit(torch.cuda.current_stream().cuda_stream))
+    except Exception as e:  # noqa: BLE001
+        ex["stability"] = {"error": repr(e)}
+    torch.cuda.empty_cache()
+    return ex
+
+
+def host_side_extras(args, np, pkg, h_keys):
+    """Host-pointer legs: pageable e2e (what every reference caller passes), the CPU baseline at the
+    full 2^28 keys (one run), the reference's own GPU path on this box (the checker, timed alone)."""
+    lib = pkg.lib()
+    n = h_keys.size
+    ex = {}
+    try:
+        work = h_keys.copy()            # ordinary pageable memory, like Go/Python/C++ callers hand in
+        assert lib.providedGpu(work.ctypes.data, n)
+        ts = []
+        for _ in range(3):
+            work[:] = h_keys
+            t0 = time.perf_counter()
+            ok = lib.providedGpu(work.ctypes.data, n)
+            ts.append(time.perf_counter() - t0)
+            assert ok
+        assert bool(np.all(work[1:] >= work[:-1]))
+        ex["e2e_pageable"] = {"value": n / (sum(ts) / len(ts)) / 1e9, "unit": UNIT, "ms_per_step": sum(ts) / len(ts) * 1e3,
+                              "h2d_bytes_per_step": 4 * n, "d2h_bytes_per_step": 4 * n,
+                              "api": "providedGpu (host pointers, pageable numpy memory)"}
+        b = np.zeros(1 << 16, np.uint32)
+        for (off, w) in ((0, 8), (0, 16)):
+            work[:] = h_keys
+            t0 = time.perf_counter()
+            ok = lib.gpuPartial(work.ctypes.data, b.ctypes.data, n, off, w)
+            ex["gpuPartial_%d_%d_pageable_ms" % (off, w)] = (time.perf_counter() - t0) * 1e3
+            assert ok
+        del work
+    except Exception as e:  # noqa: BLE001
+        ex["e2e_pageable"] = {"error": repr(e)}
+    if not args.quick:
+        try:
+            s, kind = time_cpu(h_keys, 1)
+            ex["cpu_baseline_full"] = {"value": n / s / 1e9, "unit": UNIT, "cores": 1, "kind": kind,
+                                       "sample": "the whole 2^28-key workload, one std::sort run (%.1f s)" % s}
+        except Exception as e:  # noqa: BLE001
+            ex["cpu_baseline_full"] = {"error": repr(e)}
+        try:
+            ex["reference_gpu_same_box"] = reference_gpu_same_box(np, h_keys)
+        except Exception as e:  # noqa: BLE001
+            ex["reference_gpu_same_box"] = {"error": repr(e)}
+    return ex
+
+
+def reference_gpu_same_box(np, h_keys):
+    """The reference's unmodified GPU path (oracle/_ref/libsort_ref.so, compiled for sm_100a) on the
+    same B200 and the same keys: wall time of providedGpu and gpuPartial(0,8 | 0,16) through its
+    host-pointer ABI (reference libsort/invokers.cu:15-64).  The checker's timing, reported beside
+    the product's pageable e2e -- never inside a timed region of the product."""
+    import ctypes
+    from oracle import oracle as o
+    if not o.ref_available():
+        return {"unavailable": "oracle/_ref/libsort_ref.so not built"}
+    r = o.ref()
+    u32p = ctypes.POINTER(ctypes.c_uint32)
+    if not getattr(r, "_bench_inited", False):
+        if not r.initLibSort():
+            return {"unavailable": "reference initLibSort failed"}
+        r._bench_inited = True
+    n = h_keys.size
+    out = {"keys": n, "what": "unmodified reference libsort on this GPU, host-pointer ABI, pageable memory, wall clock"}
+    work = h_keys.copy()
+    r.providedGpu(work[: 1 << 20].ctypes.data_as(u32p), 1 << 20)   # context + first-call costs out of the way
+    work[:] = h_keys
+    t0 = time.perf_counter()
+    ok = r.providedGpu(work.ctypes.data_as(u32p), n)
+    out["providedGpu_ms"] = (time.perf_counter() - t0) * 1e3
+    out["providedGpu_ok"] = bool(ok) and bool(np.all(work[1:] >= work[:-1]))
+    out["providedGpu_gkeys_s"] = n / out["providedGpu_ms"] / 1e6
+    b = np.zeros(1 << 16, np.uint32)
+    for (off, w) in ((0, 8), (0, 16)):
+        work[:] = h_keys
+        t0 = time.perf_counter()
+        ok = r.gpuPartial(work.ctypes.data_as(u32p), b.ctypes.data_as(u32p), n, off, w)
+        out["gpuPartial_%d_%d_ms" % (off, w)] = (time.perf_counter() - t0) * 1e3
+        out["gpuPartial_%d_%d_ok" % (off, w)] = bool(ok)
+    return out
+
+
 def run_single(args):
     import numpy as np
     import torch
@@ -252,6 +442,12 @@ def run_single(args):
 
     cpu_n = 1 << 26
     cpu_s, cpu_kind = time_cpu(h_keys[:cpu_n], 3)
+    extras = {}
+    if n == N_PER_GPU:
+        del d_out, d_tmp, h_work
+        torch.cuda.empty_cache()
+        extras = single_gpu_extras(args, torch, np, pkg, dev, binding, h_keys, peak)
+        extras.update(host_side_extras(args, np, pkg, h_keys))
     line = {
         "metric": METRIC, "value": n / (ms * 1e-3) / 1e9, "unit": UNIT, "n_gpus": 1, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
@@ -272,8 +468,67 @@ def run_single(args):
                                 "frac": 36.0 * n / (ms * 1e-3) / 1e9 / peak},
         "cpu_baseline": {"value": cpu_n / cpu_s / 1e9, "unit": UNIT, "cores": 1, "kind": cpu_kind,
                          "sample": "first 2^26 keys of the same PCG stream, mean of 3 std::sort runs (%.2f s each)" % cpu_s},
+        "traffic_source": "ncu --set full capture of this kernel (profiles/traffic.json); not re-measured in this run",
+        "extras": extras,
     }
     print(json.dumps(line), flush=True)
+
+
+def multi_extras(args, rank, world, sorter, distrib, torch, dist, np):
+    """BASELINE configs[4] in the same run: 2^30 skewed keys over the N GPUs (Gkeys/s + imbalance per
+    distribution), and an element-exact check at reduced size against np.sort on rank 0."""
+    ex = {}
+    n5 = (1 << 30) // world
+    rows = {}
+    for d in ("zipf", "consthigh", "consthigh16", "allequal"):
+        try:
+            k = distrib.shard_of_pcg_stream(rank, n5, d)
+            for _ in range(2):
+                sorter.sort(k)
+            torch.cuda.synchronize()
+            dist.barrier()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(5):
+                out, _ = sorter.sort_async(k) if args.exchange == "p2p" else sorter.sort(k)
+            e1.record()
+            torch.cuda.synchronize()
+            cnt = sorter._finish() if args.exchange == "p2p" else _
+            t = torch.tensor([e0.elapsed_time(e1) / 5], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            st = sorter.verify(k, out[:cnt], cnt)
+            rows[d] = {"keys_total": n5 * world, "ms_per_step": float(t), "gkeys_s": n5 * world / float(t) / 1e6,
+                       "imbalance": st["imbalance"], "verified": st["ok"]}
+            del k
+        except Exception as e:  # noqa: BLE001
+            rows[d] = {"error": repr(e)}
+    ex["c5_skew_1B"] = rows
+    ns = 1 << 22
+    L = int(ns * 1.5) + (1 << 16)
+    exact = {}
+    for d in ("uniform", "allequal", "consthigh"):
+        try:
+            k = distrib.shard_of_pcg_stream(rank, ns, d)
+            out, cnt = sorter.sort(k)
+            pad = torch.zeros(L, dtype=torch.int32, device="cuda")
+            pad[:cnt] = out[:cnt]
+            outs = torch.empty(L * world, dtype=torch.int32, device="cuda")
+            ins = torch.empty(ns * world, dtype=torch.int32, device="cuda")
+            cnts = torch.empty(world, dtype=torch.int64, device="cuda")
+            dist.all_gather_into_tensor(outs, pad)
+            dist.all_gather_into_tensor(ins, k)
+            dist.all_gather_into_tensor(cnts, torch.tensor([cnt], dtype=torch.int64, device="cuda"))
+            if rank == 0:
+                c = cnts.cpu().tolist()
+                o = outs.cpu().numpy().view(np.uint32).reshape(world, L)
+                got = np.concatenate([o[r, :c[r]] for r in range(world)])
+                want = np.sort(ins.cpu().numpy().view(np.uint32))
+                exact[d] = bool(got.size == want.size and np.array_equal(got, want))
+        except Exception as e:  # noqa: BLE001
+            exact[d] = repr(e)
+    ex["exact_small"] = {"keys_per_rank": ns, "equals_np_sort": exact}
+    return ex
 
 
 def run_multi(args, rank, world, local_rank):
@@ -321,6 +576,12 @@ def run_multi(args, rank, world, local_rank):
     phases = sorter.phase_times(d_in)               # per-phase CUDA-event times, max over ranks
     e2e = sorter.e2e(args, d_in)                    # collective: every rank takes part
     clk = clocks.stop(first=clk_first, loop_end=clk_end)
+    extras = {}
+    if args.dist == "uniform" and n == N_PER_GPU and not args.quick:
+        del d_in
+        torch.cuda.empty_cache()
+        extras = multi_extras(args, rank, world, sorter, distrib, torch, dist, np)
+        stats["exact_small"] = extras["exact_small"]["equals_np_sort"]
     if rank == 0:
         peak, peak_src = measured_peak()
         total = n * world
@@ -342,6 +603,7 @@ def run_multi(args, rank, world, local_rank):
                        "gbs_per_direction": exch_bytes / (phases["exchange_ms"] * 1e-3) / 1e9 if phases.get("exchange_ms") else None,
                        "peak_gbs": 770.0, "peak_source": "measured peer copy per direction (B200_PROFILING.md)"},
             "e2e": e2e,
+            "extras": extras,
         }
         print(json.dumps(line), flush=True)
     dist.barrier()
@@ -417,6 +679,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--quick", action="store_true", help="skip the slow extras (full-size CPU baseline, reference GPU run)")
     ap.add_argument("--keys", type=int, default=N_PER_GPU, help="keys per GPU")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
                     help="multi-GPU key exchange: fused scatter into peer memory, or NCCL all-to-all")

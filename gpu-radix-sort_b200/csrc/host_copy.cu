@@ -13,7 +13,7 @@ namespace b200sort {
 
 namespace {
 constexpr size_t kDirectBelow = 4u << 20;  // small copies: let the driver stage them
-constexpr size_t kChunk = 8u << 20;
+constexpr size_t kChunk = 2u << 20;   // LIBSORT_COPY_CHUNK_MB overrides
 
 bool ok(cudaError_t e, const char *what)
 {
@@ -35,7 +35,7 @@ bool is_pinned(const void *p)
 
 int worker_count()
 {
-    int w = 4;
+    int w = 16;  // one memcpy thread moves ~5 GB/s next to the DMA traffic: 16 x 2 MB chunks measured best (profiles/r02_pageable_copy_sweep.log)
     if (const char *e = getenv("LIBSORT_COPY_THREADS")) w = atoi(e);
     unsigned hc = std::thread::hardware_concurrency();
     if (hc && (int)hc < w) w = (int)hc;
@@ -48,6 +48,8 @@ bool HostCopier::ensure(int workers)
     if (nworkers_ >= workers) return true;
     release();
     chunk_ = kChunk;
+    if (const char *e = getenv("LIBSORT_COPY_CHUNK_MB"))
+        if (atoi(e) > 0) chunk_ = (size_t)atoi(e) << 20;
     if (!ok(cudaHostAlloc((void **)&pinned_, (size_t)workers * kSlots * chunk_, cudaHostAllocDefault), "cudaHostAlloc"))
         return false;
     for (int w = 0; w < workers; w++) {

@@ -23,7 +23,7 @@ class HostCopier {
     bool to_host(void *dst, const void *src, size_t bytes, cudaStream_t stream);
     void release();
 
-    static constexpr int kMaxWorkers = 8;
+    static constexpr int kMaxWorkers = 16;
     static constexpr int kSlots = 2;
 
   private:
