@@ -478,7 +478,7 @@ def multi_extras(args, rank, world, sorter, distrib, torch, dist, np):
     """BASELINE configs[4] in the same run: 2^30 skewed keys over the N GPUs (Gkeys/s + imbalance per
     distribution), and an element-exact check at reduced size against np.sort on rank 0."""
     ex = {}
-    n5 = (1 << 30) // world
+    n5 = min((1 << 30) // world, sorter.n_max)    # 2^30 keys in all once N >= 4; N = 2 is capped by the shard size
     rows = {}
     for d in ("zipf", "consthigh", "consthigh16", "allequal"):
         try:
@@ -504,6 +504,7 @@ def multi_extras(args, rank, world, sorter, distrib, torch, dist, np):
         except Exception as e:  # noqa: BLE001
             rows[d] = {"error": repr(e)}
     ex["c5_skew_1B"] = rows
+    ex["c5_skew_1B"]["keys_total"] = n5 * world
     ns = 1 << 22
     L = int(ns * 1.5) + (1 << 16)
     exact = {}

@@ -14,7 +14,8 @@ ADDITIVE_SYMBOLS = ["libsortTileKeys", "libsortWorkspaceBytes", "libsortDeviceSo
                     "libsortDeviceSample", "libsortDevicePickSplitters", "libsortDeviceSplitCounts", "libsortPopulateInputAt", "libsortDeviceScatterToPeers",
                     "libsortIpcAlloc", "libsortIpcFree", "libsortIpcExport", "libsortIpcOpen", "libsortIpcClose", "libsortDistribSort",
                     "libsortStepTableBytes", "libsortStepTableInit", "libsortStepCounts", "libsortStepBases", "libsortStepScatter",
-                    "libsortRankAudit", "libsortDeviceExchangePlanned", "libsortDeviceSortDyn"]
+                    "libsortRankAudit", "libsortDeviceExchangePlanned", "libsortDeviceSortDyn",
+                    "libsortDebugLastDevice", "libsortDebugPoolOverlaps"]
 
 BOUNDS_REFERENCE = 0
 BOUNDS_EXACT = 1
@@ -98,6 +99,10 @@ def lib():
     for name in ("libsortDeviceSample", "libsortDevicePickSplitters", "libsortDeviceSplitCounts", "libsortPopulateInputAt", "libsortDeviceScatterToPeers", "libsortIpcAlloc",
                  "libsortIpcFree", "libsortIpcExport", "libsortIpcOpen", "libsortIpcClose"):
         getattr(L, name).restype = ci
+    L.libsortDebugLastDevice.argtypes = []
+    L.libsortDebugLastDevice.restype = ci
+    L.libsortDebugPoolOverlaps.argtypes = []
+    L.libsortDebugPoolOverlaps.restype = ctypes.c_uint
     L.libsortRankAudit.argtypes = [vp]
     L.libsortRankAudit.restype = ci
     L.libsortDeviceExchangePlanned.argtypes = [vp, sz, vp, ci, ci, vp, vp, sz, vp, vp, vp, sz, vp]

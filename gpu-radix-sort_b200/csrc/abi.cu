@@ -62,6 +62,12 @@ struct Pool {
     bool inited = false;
 };
 Pool g_pool;
+// test hooks (libsortDebugLastDevice / libsortDebugPoolOverlaps): which GPU served this thread's last
+// host-pointer call, and how often two callers held the same GPU at once (must stay 0) -- counted
+// outside the pool mutex so that the check does not lean on the thing it checks
+thread_local int t_last_device = -1;
+std::atomic<int> g_holders[64];
+std::atomic<unsigned> g_pool_overlaps{0};
 
 bool cuda_ok(cudaError_t e, const char *what)
 {
@@ -94,6 +100,8 @@ struct Reservation {
             fprintf(stderr, "libsort: no free device after semaphore (this should not happen)\n");
             return false;
         }
+        t_last_device = c->dev;
+        if (c->dev < 64 && g_holders[c->dev].fetch_add(1) != 0) g_pool_overlaps.fetch_add(1);
         // the device is set on the calling thread, as in utils.cu:49
         if (!cuda_ok(cudaSetDevice(c->dev), "cudaSetDevice")) return false;
         if (!c->stream && !cuda_ok(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking), "cudaStreamCreate"))
@@ -103,6 +111,7 @@ struct Reservation {
     ~Reservation()
     {
         if (!c) return;
+        if (c->dev < 64) g_holders[c->dev].fetch_sub(1);
         {
             std::lock_guard<std::mutex> lk(g_pool.mu);
             c->busy = false;
@@ -397,6 +406,8 @@ API const char *libsortErrorString(int code)
 }
 
 API void libsortDebugSetPortionTiles(uint32_t tiles) { debug_set_portion_tiles(tiles); }
+API int libsortDebugLastDevice(void) { return t_last_device; }
+API unsigned libsortDebugPoolOverlaps(void) { return g_pool_overlaps.load(); }
 
 // ---- distributed-sort building blocks (include/libsort_b200.h) ----------------
 

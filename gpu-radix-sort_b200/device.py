@@ -57,3 +57,33 @@ def sort_bits(keys, offset=0, width=32, out=None, tmp=None, boundaries=False, bo
 def sort(keys, **kw):
     """Full ascending uint32 sort (device-resident providedGpu)."""
     return sort_bits(keys, 0, 32, **kw)
+
+
+def sort_dyn(keys, d_n, out=None, tmp=None, times=None):
+    """Full sort of keys[0 .. d_n[0]) where the count lives on the DEVICE (libsortDeviceSortDyn):
+    nothing is read back, launches are sized for keys.numel().  out[d_n[0]:] is left alone."""
+    _check_keys(keys)
+    if not d_n.is_cuda or d_n.dtype not in (torch.int32, torch.uint32) or d_n.numel() < 1:
+        raise ValueError("d_n must be a CUDA int32/uint32 tensor holding the key count")
+    cap = keys.numel()
+    dev = keys.device
+    out = torch.empty_like(keys) if out is None else out
+    tmp = torch.empty_like(keys) if tmp is None else tmp
+    ws = _ws(cap, dev)
+    with torch.cuda.device(dev):
+        rc = binding.lib().libsortDeviceSortDyn(
+            keys.data_ptr(), out.data_ptr(), tmp.data_ptr(), cap, d_n.data_ptr(), ws.data_ptr(), ws.numel(),
+            torch.cuda.current_stream(dev).cuda_stream, ctypes.byref(times) if times is not None else None)
+    binding.check(rc, "libsortDeviceSortDyn")
+    return out
+
+
+def rank_audit(device=None):
+    """libsortRankAudit on the current stream of `device`: True = a ranking violation was seen
+    (results since the last audit must be sorted again; the device now uses the ballot kernels)."""
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    with torch.cuda.device(dev):
+        rc = binding.lib().libsortRankAudit(torch.cuda.current_stream(dev).cuda_stream)
+    if rc < 0:
+        binding.check(rc, "libsortRankAudit")
+    return rc == 1

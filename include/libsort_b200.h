@@ -183,5 +183,10 @@ LIBSORT_API const char *libsortErrorString(int code);
 
 /* Test hook: cap tiles per look-back portion (0 restores the default). */
 LIBSORT_API void libsortDebugSetPortionTiles(uint32_t tiles);
+/* Pool test hooks: the GPU that served the calling thread's last host-pointer call (-1: none), and
+ * how many times two callers were found holding the same GPU at once (always 0; the reference
+ * reserves a device per caller, libsort/utils.cu:33-61). */
+LIBSORT_API int libsortDebugLastDevice(void);
+LIBSORT_API unsigned libsortDebugPoolOverlaps(void);
 
 #endif /* LIBSORT_B200_H */

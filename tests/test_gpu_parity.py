@@ -169,11 +169,14 @@ def test_side_by_side_with_compiled_reference(gpu_lib, oracle):
 
 
 def test_concurrent_callers(gpu_lib, oracle):
-    """16 host threads at once, full and partial, as in the reference's
-    TestParallel (benchmark/pkg/sort/libsort_test.go:35-87)."""
+    """16 host threads at once, full and partial, inside the reference's 2 s bound
+    (TestParallel, benchmark/pkg/sort/libsort_test.go:35-87, timeout at :60); no two callers ever
+    hold the same GPU (libsort/utils.cu:33-61) and each call is served by a GPU of the pool."""
+    import time
     k = oracle.pcg_stream(4099)
     want_full, (want_part, want_b) = np.sort(k), oracle.gpu_partial(k, 0, 8)
-    errs = []
+    provided_gpu(gpu_lib, k)                                   # buffers of this size exist on one GPU at least
+    errs, devs = [], []
 
     def worker(i):
         try:
@@ -182,13 +185,45 @@ def test_concurrent_callers(gpu_lib, oracle):
             else:
                 got, gb = gpu_partial(gpu_lib, k, 0, 8)
                 assert np.array_equal(got, want_part) and np.array_equal(gb, want_b)
+            devs.append(gpu_lib.libsortDebugLastDevice())
         except Exception as e:  # noqa: BLE001
             errs.append(repr(e))
 
     th = [threading.Thread(target=worker, args=(i,)) for i in range(16)]
+    t0 = time.monotonic()
     [t.start() for t in th]
-    [t.join(30) for t in th]
-    assert not errs and not any(t.is_alive() for t in th)
+    [t.join(max(0.0, 2.0 - (time.monotonic() - t0))) for t in th]
+    assert not any(t.is_alive() for t in th), "16 concurrent callers did not finish within 2 s"
+    assert not errs, errs
+    ndev = gpu_lib.libsortDeviceCount()
+    assert len(devs) == 16 and all(0 <= d < ndev for d in devs)
+    assert gpu_lib.libsortDebugPoolOverlaps() == 0
+
+
+def test_concurrent_callers_spread_over_the_pool(gpu_lib, oracle):
+    """Long enough calls (2^24 keys) from 2 x ndev threads: every GPU of the pool serves some, never
+    two callers on one GPU at a time.  On the driver's one-GPU box this is the serialised case."""
+    ndev = gpu_lib.libsortDeviceCount()
+    k = oracle.pcg_stream(1 << 24)
+    fp = (int(k.astype(np.uint64).sum()), int(np.bitwise_xor.reduce(k)))
+    devs, errs = [], []
+
+    def worker():
+        try:
+            x = provided_gpu(gpu_lib, k)
+            assert bool(np.all(x[1:] >= x[:-1])) and (int(x.astype(np.uint64).sum()), int(np.bitwise_xor.reduce(x))) == fp
+            devs.append(gpu_lib.libsortDebugLastDevice())
+        except Exception as e:  # noqa: BLE001
+            errs.append(repr(e))
+
+    for _ in range(2):                                        # first round allocates per-GPU buffers
+        devs.clear()
+        th = [threading.Thread(target=worker) for _ in range(2 * ndev)]
+        [t.start() for t in th]
+        [t.join(120) for t in th]
+        assert not errs and not any(t.is_alive() for t in th), errs
+    assert set(devs) == set(range(ndev)), devs
+    assert gpu_lib.libsortDebugPoolOverlaps() == 0
 
 
 def test_second_init_fails_and_oversize_rejected(gpu_lib):
