@@ -57,6 +57,16 @@ namespace b200sort {
 #define HIST_REPL 2
 #endif
 
+// Small inputs (<= kSmallNMax keys): the same scatter kernel with 16 keys per thread.  A 1 M-key
+// sort is 73 big tiles -- half the SMs idle, every pass one long tile -- but 256 small ones.
+#ifndef SMALL_KPT
+#define SMALL_KPT 16
+#endif
+#ifndef SMALL_MINB
+#define SMALL_MINB 4
+#endif
+constexpr int kTileS = SORT_THREADS * SMALL_KPT;
+constexpr size_t kSmallNMax = (size_t)1 << 21;
 constexpr int kTileA = SORT_THREADS * SORT_KPT;
 constexpr int kTileB = SORT_THREADS * BALLOT_KPT;
 constexpr int kTileMin = kTileA < kTileB ? kTileA : kTileB;
@@ -65,6 +75,8 @@ using SmemB = OnesweepSmem<SORT_THREADS, BALLOT_KPT, false, RadixBinner::Arg>;
 using SmemSplit = OnesweepSmem<SORT_THREADS, BALLOT_KPT, true, SplitArg>;
 
 #define KERNEL_A(NBITS) k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, RANK_ATOMS, NBITS, SORT_LB, RadixBinner, false>
+#define KERNEL_S(NBITS) k_onesweep<SORT_THREADS, SMALL_KPT, SMALL_MINB, RANK_ATOMS, NBITS, SORT_LB, RadixBinner, false>
+using SmemS = OnesweepSmem<SORT_THREADS, SMALL_KPT, false, RadixBinner::Arg>;
 #define KERNEL_BULK k_onesweep_bulk<SORT_THREADS, SORT_KPT, SORT_MINB, SORT_LB, RANK_ATOMS, RadixBinner, false>
 using SmemBulk = BulkSmem<SORT_THREADS, SORT_KPT, RadixBinner::Arg>;
 #define KERNEL_SPLIT_BULK(NS) k_onesweep_bulk<SORT_THREADS, SPLIT_KPT, SPLIT_BULK_MINB, SORT_LB, RANK_BALLOT, SplitBinner<NS>, true>
@@ -153,13 +165,15 @@ static size_t num_tiles(size_t n, int tile) { return (n + tile - 1) / tile; }
 
 size_t workspace_bytes(size_t n)
 {
-    return (WS_DESC + (size_t)MAX_PASSES * num_tiles(n, kTileMin) * RADIX) * sizeof(uint32_t);
+    const size_t tiles = std::max(num_tiles(n, kTileMin), n <= kSmallNMax ? num_tiles(n, kTileS) : (size_t)0);
+    return (WS_DESC + (size_t)MAX_PASSES * tiles * RADIX) * sizeof(uint32_t);
 }
 
 // ---- per-device launch parameters -----------------------------------------
 struct DevInfo {
     bool ready = false;
     int sms = 0;
+    int occ_s = 0;  // the small-input scatter kernel
     int occ_a = 0, occ_b = 0, occ_split = 0, occ_bulk = 0, occ_split_bulk = 0;  // resident CTAs per SM of the three scatter kernels
     int occ_sliced_a = 0, occ_sliced_b = 0;
     int occ_k3[32] = {};
@@ -178,6 +192,8 @@ static int env_int(const char *name, int dflt)
 static const int g_hist_mode = env_int("LIBSORT_HIST_MODE", 1);
 // 1 = bulk-copy write-out of the scatter pass (k_onesweep_bulk), 0 = LDS + STG write-out (k_onesweep)
 static const int g_bulk_out = env_int("LIBSORT_BULK_OUT", 0);
+static const int g_pdl = env_int("LIBSORT_PDL", 1);  // programmatic dependent launch between the kernels of one sort
+static const int g_small_path = env_int("LIBSORT_SMALL_PATH", 1);  // 0: big tiles at every size (A/B measurements)
 // the same choice for the splitter scatter of the distributed sort (runs of kilobytes, peer destinations)
 static const int g_bulk_exchange = env_int("LIBSORT_BULK_EXCHANGE", 1);
 // 1 = the planned exchange keeps the tiles of a destination in shard order (look-back), 0 = cursor atomics
@@ -239,6 +255,26 @@ static cudaError_t choose_rank_mode(int dev, bool *atoms)
     return cudaSuccess;
 }
 
+// Launch `kern` so that it may begin while the previous kernel of the stream is still draining
+// (programmatic dependent launch): the kernel itself calls pdl_wait() before it reads anything the
+// predecessor wrote.  Cuts the ~4 us launch gap between the 6-7 kernels of one sort, which is
+// most of a small sort's time.
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_after(void (*kern)(KArgs...), int grid, int block, size_t smem, cudaStream_t st, Args... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3((unsigned)block);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = g_pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
 static cudaError_t dev_info(DevInfo **out)
 {
     int dev = 0;
@@ -252,6 +288,7 @@ static cudaError_t dev_info(DevInfo **out)
         if (e != cudaSuccess) return e;
         struct { const void *fn; int smem; } kernels[] = {
             {(const void *)KERNEL_A(8), (int)sizeof(SmemA)},     {(const void *)KERNEL_A(0), (int)sizeof(SmemA)},
+            {(const void *)KERNEL_S(8), (int)sizeof(SmemS)},     {(const void *)KERNEL_S(0), (int)sizeof(SmemS)},
             {(const void *)KERNEL_BULK, (int)sizeof(SmemBulk)},
             {(const void *)KERNEL_SPLIT_BULK(1), (int)sizeof(SmemSplitBulk)}, {(const void *)KERNEL_SPLIT_BULK(3), (int)sizeof(SmemSplitBulk)},
             {(const void *)KERNEL_SPLIT_BULK(7), (int)sizeof(SmemSplitBulk)}, {(const void *)KERNEL_SPLIT_BULK(15), (int)sizeof(SmemSplitBulk)},
@@ -275,6 +312,8 @@ static cudaError_t dev_info(DevInfo **out)
             }
         }
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.occ_a, KERNEL_A(8), SORT_THREADS, sizeof(SmemA));
+        if (e != cudaSuccess) return e;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.occ_s, KERNEL_S(8), SORT_THREADS, sizeof(SmemS));
         if (e != cudaSuccess) return e;
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.occ_bulk, KERNEL_BULK, SORT_THREADS, sizeof(SmemBulk));
         if (e != cudaSuccess) return e;
@@ -425,7 +464,10 @@ cudaError_t sort_bits(const uint32_t *in, uint32_t *a, uint32_t *b, uint32_t *wa
     // dyn_n (key count read on the device, n = capacity): plain kernels, one look-back portion, no boundaries
     if (dyn_n && (d_bounds || n >= (1ull << 30))) return cudaErrorInvalidValue;
     const int k3 = (!dyn_n && dev->rank_atoms && k3_selected() >= 0 && dev->occ_k3[k3_selected()] > 0) ? k3_selected() : -1;
-    const int tile = k3 >= 0 ? g_k3[k3].tile : dev->rank_atoms ? kTileA : kTileB;
+    // small input: more, shorter tiles (not with the debug portion override, whose tests count big tiles)
+    const bool small = g_small_path && !dyn_n && k3 < 0 && dev->rank_atoms && dev->occ_s > 0 && n <= kSmallNMax &&
+                       n < (size_t)dev->sms * kTileA && g_portion_tiles.load() == 0;
+    const int tile = small ? kTileS : k3 >= 0 ? g_k3[k3].tile : dev->rank_atoms ? kTileA : kTileB;
     const size_t ntiles = num_tiles(n, tile);
     const uint32_t ptiles = portion_tiles(tile);
     const size_t nportions = (ntiles + ptiles - 1) / ptiles;
@@ -434,6 +476,7 @@ cudaError_t sort_bits(const uint32_t *in, uint32_t *a, uint32_t *b, uint32_t *wa
     Timer tm(st, times != nullptr);
     int launches = 0;
     tm.mark();
+    const bool bounds_from_hist = d_bounds && P == 1 && plan.mask[0] == ngroups - 1;
     CK(cudaMemsetAsync(ws, 0, (WS_DESC + (size_t)P * ntiles * RADIX) * sizeof(uint32_t), st));
     tm.mark();
 
@@ -446,10 +489,9 @@ cudaError_t sort_bits(const uint32_t *in, uint32_t *a, uint32_t *b, uint32_t *wa
     }
     launches++;
     tm.mark();
-    const bool bounds_from_hist = d_bounds && P == 1 && plan.mask[0] == ngroups - 1;
     // constant-digit passes become copies (single-portion inputs only: the copy's destination is `dst` itself)
-    k_scan_hist<<<P, RADIX, 0, st>>>(ghist, base, bounds_from_hist ? d_bounds : nullptr, (uint32_t)ngroups, (uint32_t)n,
-                                     nportions == 1 ? tickets + SKIP_OFFSET : nullptr, dyn_n);
+    CK(launch_after(k_scan_hist, P, RADIX, 0, st, ghist, base, bounds_from_hist ? d_bounds : nullptr, (uint32_t)ngroups, (uint32_t)n,
+                    nportions == 1 ? tickets + SKIP_OFFSET : nullptr, dyn_n));
     launches++;
     tm.mark();
 
@@ -476,7 +518,12 @@ cudaError_t sort_bits(const uint32_t *in, uint32_t *a, uint32_t *b, uint32_t *wa
             const bool full_digit = plan.mask[p] == 0xffu;
             const RadixBinner::Arg barg{plan.shift[p], plan.mask[p]};
             uint32_t *dsc = desc + ((size_t)p * ntiles + t0) * RADIX, *tk = tickets + p * MAX_PORTIONS + q;
-            if (k3 >= 0) {
+            if (small) {
+                auto kern = full_digit ? KERNEL_S(8) : KERNEL_S(0);
+                CK(launch_after(kern, (int)std::min<size_t>(nt, (size_t)dev->sms * dev->occ_s), SORT_THREADS, sizeof(SmemS), st,
+                                src + k0, dst, (uint32_t)(k1 - k0), barg, (const void *)bcur, bnext, dsc, tk, nt, use_tma,
+                                (const uint32_t *)nullptr));
+            } else if (k3 >= 0) {
                 const int gridk = (int)std::min<size_t>(nt, (size_t)dev->sms * dev->occ_k3[k3]);
                 g_k3[k3].fn<<<gridk, g_k3[k3].threads, g_k3[k3].smem, st>>>(src + k0, dst, (uint32_t)(k1 - k0), barg, bcur, bnext, dsc, tk,
                                                                            nt, use_tma);
@@ -487,7 +534,8 @@ cudaError_t sort_bits(const uint32_t *in, uint32_t *a, uint32_t *b, uint32_t *wa
             } else {
                 auto kern = dev->rank_atoms ? (full_digit ? KERNEL_A(8) : KERNEL_A(0)) : (full_digit ? KERNEL_B(8) : KERNEL_B(0));
                 const size_t smem = dev->rank_atoms ? sizeof(SmemA) : sizeof(SmemB);
-                kern<<<grid, SORT_THREADS, smem, st>>>(src + k0, dst, (uint32_t)(k1 - k0), barg, bcur, bnext, dsc, tk, nt, use_tma, dyn_n);
+                CK(launch_after(kern, grid, SORT_THREADS, smem, st, src + k0, dst, (uint32_t)(k1 - k0), barg, (const void *)bcur, bnext,
+                                dsc, tk, nt, use_tma, dyn_n));
             }
             launches++;
         }

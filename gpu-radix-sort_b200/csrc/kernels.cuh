@@ -190,6 +190,8 @@ __global__ void __launch_bounds__(256) k_scan_hist(const uint32_t *__restrict__ 
                                                   uint32_t *__restrict__ skip, const uint32_t *__restrict__ dyn_n)
 {
     __shared__ uint32_t s_warp[8];
+    pdl_wait();  // K1's counts (programmatic dependent launch, engine.cu launch_after)
+    pdl_trigger();
     if (dyn_n) n = *dyn_n;
     const int p = blockIdx.x;
     uint32_t c = ghist[p * RADIX + threadIdx.x];
@@ -469,10 +471,6 @@ __global__ void __launch_bounds__(THREADS, MINB)
                uint32_t *__restrict__ ticket, uint32_t ntiles, int use_tma, const uint32_t *__restrict__ dyn_n)
 {
     using Smem = OnesweepSmem<THREADS, KPT, PTR_OUT, typename Binner::Arg>;
-    if (dyn_n) {  // key count decided on the device: the grid and the descriptors were sized for the capacity
-        n = *dyn_n;
-        ntiles = (n + (uint32_t)(THREADS * KPT) - 1u) / (uint32_t)(THREADS * KPT);
-    }
     static_assert(!(RANK == RANK_ATOMS && Binner::kByPosition), "the heavy-tile path bins by key alone");
     constexpr int TILE = Smem::TILE;
     constexpr int NWARPS = Smem::NWARPS;
@@ -480,11 +478,26 @@ __global__ void __launch_bounds__(THREADS, MINB)
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Smem &s = *reinterpret_cast<Smem *>(smem_raw);
 
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // Prologue that touches no global memory (barrier init, counters zeroed): under a programmatic
+    // dependent launch it runs while the previous pass drains.  Everything after pdl_wait() sees the
+    // previous kernel's keys, bases, tickets and descriptors.
+    if (tid == 0) {
+        mbar_init(&s.mbar, 1);
+        fence_mbar_init();
+    }
+#pragma unroll
+    for (int j = lane; j < RADIX; j += 32) s.warp_hist[warp][j] = 0;
+    pdl_wait();
+    pdl_trigger();
+    if (dyn_n) {  // key count decided on the device: the grid and the descriptors were sized for the capacity
+        n = *dyn_n;
+        ntiles = (n + (uint32_t)(THREADS * KPT) - 1u) / (uint32_t)(THREADS * KPT);
+    }
     if (PTR_OUT == OUT_INDEX && ticket[SKIP_OFFSET]) {  // constant digit (k_scan_hist): the pass is a copy
         copy_keys(in, out, n);
         return;
     }
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const Binner binner(binner_arg);
     const uint32_t pad_bin = binner.pad_bin();
     unsigned char *const my_hist = reinterpret_cast<unsigned char *>(s.warp_hist[warp]);
@@ -505,8 +518,6 @@ __global__ void __launch_bounds__(THREADS, MINB)
     };
 
     if (tid == 0) {
-        mbar_init(&s.mbar, 1);
-        fence_mbar_init();
         const uint32_t t = atomicAdd(ticket, 1u);
         s.next_tile = t;
         s.binner_arg = binner_arg;
@@ -518,8 +529,6 @@ __global__ void __launch_bounds__(THREADS, MINB)
         if (tid <= MAX_SLICES) s.slice_start[tid] = tab->slice_start[tid];
         if (tid == 0) s.nslice = tab->nslice;
     }
-#pragma unroll
-    for (int j = lane; j < RADIX; j += 32) s.warp_hist[warp][j] = 0;
     __syncthreads();
     uint32_t cur = s.next_tile;
 

@@ -9,8 +9,8 @@ if [ "${1:-tests}" = "tests" ]; then
 timeout 600 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err
 timeout 300 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.json 2>> gpurun_out/bench.err
 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/smoke.log 2>&1; tail -1 gpurun_out/smoke.log
-python bench.py --steps 2 --warmup 1 > gpurun_out/plain_bench.log 2>&1 && \
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 1 > gpurun_out/ncu_launches.log 2>&1
+python bench.py --quick --steps 2 --warmup 1 > gpurun_out/plain_bench.log 2>&1 && \
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv python bench.py --quick --steps 2 --warmup 1 > gpurun_out/ncu_launches.log 2>&1
 rm -f gpurun_out/devbench_sizes.log
 for n in 1048576 268435456 536870912; do $D time $n 10 >> gpurun_out/devbench_sizes.log 2>&1; done
 tail -3 gpurun_out/pytest_gpu.log; cat gpurun_out/bench.json gpurun_out/bench_ref.json; cat gpurun_out/devbench_sizes.log
