@@ -574,6 +574,7 @@ def run_multi(args, rank, world, local_rank):
     dist.all_reduce(ms_local, op=dist.ReduceOp.MAX)
     ms = float(ms_local.item())
     stats = sorter.verify(d_in, out, cnt)           # sortedness, rank ordering, multiset fingerprint
+    stats["rank_audit_violation"] = bool(getattr(sorter, "rank_violation", False))   # max over ranks (DistributedSorter._finish)
     phases = sorter.phase_times(d_in)               # per-phase CUDA-event times, max over ranks
     e2e = sorter.e2e(args, d_in)                    # collective: every rank takes part
     clk = clocks.stop(first=clk_first, loop_end=clk_end)

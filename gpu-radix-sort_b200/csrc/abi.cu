@@ -682,19 +682,32 @@ API int libsortDistribSort(uint32_t *h_keys, size_t n, int ngpu)
     }
     if (!dist_sync_all(cs, P, "sync(exchange)")) return 0;  // every store has landed before anyone sorts
 
-    // 5. local sort of what arrived, straight back into the caller's array (GPU d owns the d-th value range)
+    // 5. local sort of what arrived (GPU d owns the d-th value range): all GPUs sort at once, then each result is
+    //    audited (atomic-ranking check, include/libsort_b200.h libsortRankAudit; the received keys are still
+    //    intact in c.recv, so a violation just repeats the sort with the ballot kernels) and goes straight
+    //    back into the caller's array
+    uint32_t *sorted[kDistMaxGpus] = {};
+    auto local_sort = [&](int d) {
+        DeviceCtx &c = *cs[d];
+        return cuda_ok(sort_bits(c.recv, c.a, c.b, nullptr, totals[d], 0, 32, nullptr, BOUNDS_EXACT, c.ws, c.ws_cap, c.stream,
+                                 &sorted[d], nullptr),
+                       "local sort");
+    };
+    for (int d = 0; d < P; d++) {
+        if (!totals[d]) continue;
+        if (!cuda_ok(cudaSetDevice(cs[d]->dev), "cudaSetDevice")) return 0;
+        if (!ensure_capacity(*cs[d], totals[d], 0)) return 0;  // the shard in c.a is no longer needed
+        if (!local_sort(d)) return 0;
+    }
     size_t first = 0;
     for (int d = 0; d < P; d++) {
         DeviceCtx &c = *cs[d];
-        if (!cuda_ok(cudaSetDevice(c.dev), "cudaSetDevice")) return 0;
         if (totals[d]) {
-            if (!ensure_capacity(c, totals[d], 0)) return 0;  // the shard in c.a is no longer needed
-            uint32_t *res = nullptr;
-            if (!cuda_ok(sort_bits(c.recv, c.a, c.b, nullptr, totals[d], 0, 32, nullptr, BOUNDS_EXACT, c.ws, c.ws_cap,
-                                   c.stream, &res, nullptr),
-                         "local sort"))
-                return 0;
-            if (!c.copier.to_host(h_keys + first, res, totals[d] * sizeof(uint32_t), c.stream)) return 0;
+            if (!cuda_ok(cudaSetDevice(c.dev), "cudaSetDevice")) return 0;
+            bool violated = false;
+            if (!cuda_ok(rank_audit(c.stream, &violated), "rank audit")) return 0;
+            if (violated && !local_sort(d)) return 0;
+            if (!c.copier.to_host(h_keys + first, sorted[d], totals[d] * sizeof(uint32_t), c.stream)) return 0;
         }
         first += totals[d];
     }

@@ -140,6 +140,7 @@ class DistributedSorter:
         self.launches_per_sort = 1 + 6 + 1 + 1 + 1 + 1 + 6
         self.launches_per_stepwise_sort = 4 * 3    # per step: histogram, bases, scatter
         self.last_totals = None
+        self.rank_violation = False
 
     def close(self):
         if self._step is not None:
@@ -237,6 +238,15 @@ class DistributedSorter:
             self.d_status.zero_()
             raise RuntimeError("receive buffer too small: %d keys arrive, capacity %d (raise slack)"
                                % (int(self.last_totals.max()), self.cap))
+        # atomic-ranking audit (include/libsort_b200.h libsortRankAudit): a violation on ANY rank makes
+        # every rank's result suspect; the ranks agree on the verdict so that they repeat together
+        rc = self.lib.libsortRankAudit(self._stream())
+        if rc < 0:
+            binding.check(rc, "libsortRankAudit")
+        flag = torch.tensor([rc], dtype=torch.int32, device=self.dev)
+        if W > 1:
+            dist.all_reduce(flag, op=dist.ReduceOp.MAX, group=self.group)
+        self.rank_violation = bool(int(flag.item()))
         return nrecv
 
     def sort(self, keys, ev=None, times=None):
@@ -247,8 +257,11 @@ class DistributedSorter:
         if n > self.n_max:
             raise ValueError("shard larger than the sorter was built for")
         if self.mode == "p2p":
-            out, _ = self.sort_async(keys, ev=ev, times=times)
-            nrecv = self._finish()
+            for _attempt in range(2):       # `keys` is untouched: after a ranking violation sort it again (ballot kernels)
+                out, _ = self.sort_async(keys, ev=ev, times=times)
+                nrecv = self._finish()
+                if not self.rank_violation:
+                    break
             return out[:nrecv], nrecv
         cm = self._plan(keys, ev)
         offsets, totals = distrib_plan.recv_layout(cm)
