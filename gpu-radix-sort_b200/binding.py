@@ -15,7 +15,7 @@ ADDITIVE_SYMBOLS = ["libsortTileKeys", "libsortWorkspaceBytes", "libsortDeviceSo
                     "libsortIpcAlloc", "libsortIpcFree", "libsortIpcExport", "libsortIpcOpen", "libsortIpcClose", "libsortDistribSort",
                     "libsortStepTableBytes", "libsortStepTableInit", "libsortStepCounts", "libsortStepBases", "libsortStepScatter",
                     "libsortRankAudit", "libsortDeviceExchangePlanned", "libsortDeviceSortDyn",
-                    "libsortDebugLastDevice", "libsortDebugPoolOverlaps"]
+                    "libsortDebugLastDevice", "libsortDebugPoolOverlaps", "libsortDeviceExchangeCursor"]
 
 BOUNDS_REFERENCE = 0
 BOUNDS_EXACT = 1
@@ -107,6 +107,8 @@ def lib():
     L.libsortRankAudit.restype = ci
     L.libsortDeviceExchangePlanned.argtypes = [vp, sz, vp, ci, ci, vp, vp, sz, vp, vp, vp, sz, vp]
     L.libsortDeviceExchangePlanned.restype = ci
+    L.libsortDeviceExchangeCursor.argtypes = [vp, sz, vp, ci, vp, sz, vp, vp, sz, vp]
+    L.libsortDeviceExchangeCursor.restype = ci
     L.libsortDeviceSortDyn.argtypes = [vp, vp, vp, sz, vp, vp, sz, vp, ctypes.POINTER(KernelTimes)]
     L.libsortDeviceSortDyn.restype = ci
     L.libsortDistribSort.argtypes = [vp, sz, ci]

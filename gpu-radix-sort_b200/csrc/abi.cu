@@ -469,6 +469,14 @@ API int libsortDeviceExchangePlanned(const uint32_t *d_in, size_t n, const uint3
                                  d_workspace, workspace_len, (cudaStream_t)stream);
 }
 
+API int libsortDeviceExchangeCursor(const uint32_t *d_in, size_t n, const uint32_t *splitters, int nranks,
+                                    const unsigned long long *d_peer_bases, size_t cap, uint32_t *d_status,
+                                    void *d_workspace, size_t workspace_len, void *stream)
+{
+    return (int)exchange_cursor(d_in, n, splitters, nranks, d_peer_bases, cap, d_status, d_workspace, workspace_len,
+                                (cudaStream_t)stream);
+}
+
 API int libsortDeviceSortDyn(const uint32_t *d_in, uint32_t *d_out, uint32_t *d_tmp, size_t capacity, const uint32_t *d_n,
                              void *d_workspace, size_t workspace_len, void *stream, LibsortKernelTimes *times)
 {

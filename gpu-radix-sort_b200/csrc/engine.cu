@@ -81,7 +81,9 @@ using SmemS = OnesweepSmem<SORT_THREADS, SMALL_KPT, false, RadixBinner::Arg>;
 using SmemBulk = BulkSmem<SORT_THREADS, SORT_KPT, RadixBinner::Arg>;
 #define KERNEL_SPLIT_BULK(NS) k_onesweep_bulk<SORT_THREADS, SPLIT_KPT, SPLIT_BULK_MINB, SORT_LB, RANK_BALLOT, SplitBinner<NS>, true>
 #define KERNEL_SPLIT_BULK_UNORDERED(NS) \
-    k_onesweep_bulk<SORT_THREADS, SPLIT_KPT, SPLIT_BULK_MINB, SORT_LB, RANK_BALLOT, SplitBinner<NS>, true, true>
+    k_onesweep_bulk<SORT_THREADS, SPLIT_KPT, SPLIT_BULK_MINB, SORT_LB, RANK_BALLOT, SplitBinner<NS>, true, EXCH_LOCAL_CURSOR>
+#define KERNEL_SPLIT_BULK_REMOTE(NS) \
+    k_onesweep_bulk<SORT_THREADS, SPLIT_KPT, SPLIT_BULK_MINB, SORT_LB, RANK_BALLOT, SplitBinner<NS>, true, EXCH_REMOTE_CURSOR>
 using SmemSplitBulk = BulkSmem<SORT_THREADS, SPLIT_KPT, SplitArg>;
 constexpr int kTileSplitBulk = SORT_THREADS * SPLIT_KPT;
 #define KERNEL_B(NBITS) k_onesweep<SORT_THREADS, BALLOT_KPT, BALLOT_MINB, RANK_BALLOT, NBITS, SORT_LB, RadixBinner, false>
@@ -294,6 +296,8 @@ static cudaError_t dev_info(DevInfo **out)
             {(const void *)KERNEL_SPLIT_BULK(7), (int)sizeof(SmemSplitBulk)}, {(const void *)KERNEL_SPLIT_BULK(15), (int)sizeof(SmemSplitBulk)},
             {(const void *)KERNEL_SPLIT_BULK_UNORDERED(1), (int)sizeof(SmemSplitBulk)}, {(const void *)KERNEL_SPLIT_BULK_UNORDERED(3), (int)sizeof(SmemSplitBulk)},
             {(const void *)KERNEL_SPLIT_BULK_UNORDERED(7), (int)sizeof(SmemSplitBulk)}, {(const void *)KERNEL_SPLIT_BULK_UNORDERED(15), (int)sizeof(SmemSplitBulk)},
+            {(const void *)KERNEL_SPLIT_BULK_REMOTE(1), (int)sizeof(SmemSplitBulk)}, {(const void *)KERNEL_SPLIT_BULK_REMOTE(3), (int)sizeof(SmemSplitBulk)},
+            {(const void *)KERNEL_SPLIT_BULK_REMOTE(7), (int)sizeof(SmemSplitBulk)}, {(const void *)KERNEL_SPLIT_BULK_REMOTE(15), (int)sizeof(SmemSplitBulk)},
             {(const void *)KERNEL_B(8), (int)sizeof(SmemB)},     {(const void *)KERNEL_B(0), (int)sizeof(SmemB)},
             {(const void *)KERNEL_SPLIT(1), (int)sizeof(SmemSplit)},  {(const void *)KERNEL_SPLIT(3), (int)sizeof(SmemSplit)},
             {(const void *)KERNEL_SPLIT(7), (int)sizeof(SmemSplit)},  {(const void *)KERNEL_SPLIT(15), (int)sizeof(SmemSplit)},
@@ -708,6 +712,35 @@ cudaError_t exchange_planned(const uint32_t *in, size_t n, const uint32_t *split
         kern<<<grid, SORT_THREADS, sizeof(SmemSplit), st>>>(in, nullptr, (uint32_t)n, arg, d_ptrs, nullptr, ws + WS_DESC,
                                                             ws + WS_TICKET, (uint32_t)ntiles, use_tma, nullptr);
     }
+    return cudaGetLastError();
+}
+
+cudaError_t exchange_cursor(const uint32_t *in, size_t n, const uint32_t *splitters, int nranks,
+                            const unsigned long long *d_peer_bases, size_t cap, uint32_t *d_status, void *workspace,
+                            size_t workspace_len, cudaStream_t st)
+{
+    if (nranks < 1 || nranks > MAX_SPLITTERS + 1 || n >= (1ull << 30) || cap >= (1ull << 32)) return cudaErrorInvalidValue;
+    if (workspace_len < workspace_bytes(n) || !workspace) return cudaErrorInvalidValue;
+    DevInfo *dev = nullptr;
+    CK(dev_info(&dev));
+    if (dev->occ_split_bulk < 1) return cudaErrorLaunchOutOfResources;
+    uint32_t *ws = static_cast<uint32_t *>(workspace);
+    const size_t ntiles = num_tiles(n, kTileSplitBulk);
+    static_assert(sizeof(CursorPlan) <= (WS_TICKET - WS_HIST) * sizeof(uint32_t), "the plan lives in the histogram words");
+    CK(cudaMemsetAsync(ws + WS_TICKET, 0, 64 * sizeof(uint32_t), st));  // the tile ticket; no descriptors in this mode
+    CursorPlan *plan = reinterpret_cast<CursorPlan *>(ws + WS_HIST);
+    k_store_cursor_plan<<<1, 32, 0, st>>>(d_peer_bases, nranks, (unsigned long long)cap, d_status, plan);
+    if (n == 0) return cudaGetLastError();
+    const int nsplit = nranks - 1;
+    const int use_tma = (reinterpret_cast<uintptr_t>(in) & 15u) == 0;
+    const SplitArg arg{splitters, nsplit};
+    auto kern = nsplit <= 1   ? KERNEL_SPLIT_BULK_REMOTE(1)
+                : nsplit <= 3 ? KERNEL_SPLIT_BULK_REMOTE(3)
+                : nsplit <= 7 ? KERNEL_SPLIT_BULK_REMOTE(7)
+                              : KERNEL_SPLIT_BULK_REMOTE(15);
+    const int gridb = (int)std::min<size_t>(ntiles, (size_t)dev->sms * dev->occ_split_bulk);
+    kern<<<gridb, SORT_THREADS, sizeof(SmemSplitBulk), st>>>(in, nullptr, (uint32_t)n, arg, plan, nullptr, ws + WS_DESC, ws + WS_TICKET,
+                                                             (uint32_t)ntiles, use_tma);
     return cudaGetLastError();
 }
 

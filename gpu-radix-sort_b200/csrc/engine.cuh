@@ -95,6 +95,15 @@ cudaError_t exchange_planned(const uint32_t *in, size_t n, const uint32_t *split
                              uint32_t *d_nrecv, uint32_t *d_status, void *workspace, size_t workspace_len,
                              cudaStream_t st);
 
+// The exchange without any plan: every receive buffer is followed by its cursor word (at key index
+// `cap`), zero before the exchange; sources reserve room for each tile's run with a system-scope
+// atomicAdd on the destination's cursor (NVLink), so no rank needs to know any counts beforehand.
+// Afterwards (all ranks done) the cursor = keys received.  *d_status is raised when a reservation
+// would pass `cap` (those keys are dropped; the destination's cursor then exceeds cap).
+cudaError_t exchange_cursor(const uint32_t *in, size_t n, const uint32_t *splitters, int nranks,
+                            const unsigned long long *d_peer_bases, size_t cap, uint32_t *d_status, void *workspace,
+                            size_t workspace_len, cudaStream_t st);
+
 // Test hook: cap the number of tiles per look-back portion (0 = default,
 // i.e. the largest portion whose key count fits the 30-bit descriptors).
 void debug_set_portion_tiles(uint32_t tiles);

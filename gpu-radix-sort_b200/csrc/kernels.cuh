@@ -54,7 +54,7 @@ __global__ void __launch_bounds__(THREADS) k_histogram(const uint32_t *__restric
                                                       uint32_t *__restrict__ ghist, const uint32_t *__restrict__ dyn_n)
 {
     __shared__ uint32_t s_hist[REPL][NPASS][RADIX];
-    if (dyn_n) n = *dyn_n;  // key count decided on the device (the launch was sized for the capacity)
+    if (dyn_n) n = min((size_t)*dyn_n, n);  // key count decided on the device (the launch was sized for the capacity = n)
     for (int i = threadIdx.x; i < REPL * NPASS * RADIX; i += THREADS) (&s_hist[0][0][0])[i] = 0;
     __syncthreads();
 
@@ -111,7 +111,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_histogram_lanes(const uint32_t *
                                                                uint32_t *__restrict__ ghist, const uint32_t *__restrict__ dyn_n)
 {
     extern __shared__ __align__(16) uint32_t s_lane_hist[];  // [NPASS][RADIX][32]
-    if (dyn_n) n = *dyn_n;
+    if (dyn_n) n = min((size_t)*dyn_n, n);
     for (int i = threadIdx.x; i < NPASS * RADIX * 32; i += THREADS) s_lane_hist[i] = 0;
     __syncthreads();
     const uint32_t lane = threadIdx.x & 31;
@@ -192,7 +192,7 @@ __global__ void __launch_bounds__(256) k_scan_hist(const uint32_t *__restrict__ 
     __shared__ uint32_t s_warp[8];
     pdl_wait();  // K1's counts (programmatic dependent launch, engine.cu launch_after)
     pdl_trigger();
-    if (dyn_n) n = *dyn_n;
+    if (dyn_n) n = min(*dyn_n, n);  // never past the capacity the launch was sized for
     const int p = blockIdx.x;
     uint32_t c = ghist[p * RADIX + threadIdx.x];
     uint32_t ex = block_excl_scan_256(c, s_warp, nullptr);
@@ -491,7 +491,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
     pdl_wait();
     pdl_trigger();
     if (dyn_n) {  // key count decided on the device: the grid and the descriptors were sized for the capacity
-        n = *dyn_n;
+        n = min(*dyn_n, n);  // never past the capacity the launch was sized for
         ntiles = (n + (uint32_t)(THREADS * KPT) - 1u) / (uint32_t)(THREADS * KPT);
     }
     if (PTR_OUT == OUT_INDEX && ticket[SKIP_OFFSET]) {  // constant digit (k_scan_hist): the pass is a copy

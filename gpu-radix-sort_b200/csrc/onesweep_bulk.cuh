@@ -48,7 +48,40 @@ struct BulkSmem {
 // range -- the distributed sort sorts what arrived anyway -- so a tile reserves its place with ONE
 // atomicAdd per destination on a cursor array (`desc`, 16 zeroed words) instead of waiting, fully
 // exposed here, for the look-back over all earlier tiles.
-template <int THREADS, int KPT, int MINB, int LB, int RANK, class Binner, bool PTR_OUT, bool UNORDERED = false>
+// UNORDERED == EXCH_REMOTE_CURSOR: the cursors are not a local array but one word PER DESTINATION BUFFER,
+// living on the destination GPU (base_v = CursorPlan): every source reserves room for a tile's run
+// with one system-scope atomicAdd over NVLink.  Nobody needs to know in advance how many keys go
+// where -- no counting pass, no count exchange -- and when all sources are done the word holds the
+// number of keys received.  A reservation that would pass the buffer's capacity is dropped and
+// raises *status (the word still counts it, so the receiver sees cursor > capacity).
+// (Measured and dropped: reserving whole 16-byte chunks, runs padded with 0xFFFFFFFF, so that the
+// layout does not wait for the atomic -- the exchange was no faster, 0.948 vs 0.956 ms at 2 GPUs, and
+// the padding keys spoil the constant-digit and heavy-tile shortcuts of the local sort on skewed
+// inputs: all-equal keys 5.07 ms instead of 3.55 ms per sort.)
+constexpr int EXCH_ORDERED = 0, EXCH_LOCAL_CURSOR = 1, EXCH_REMOTE_CURSOR = 2;
+struct CursorPlan {
+    unsigned long long dest[MAX_SPLITTERS + 1];    // receive buffer of every rank as mapped here
+    unsigned long long cursor[MAX_SPLITTERS + 1];  // its cursor word
+    uint32_t cap;                                  // keys a receive buffer holds
+    uint32_t unused;
+    uint32_t *status;                              // local overflow flag
+};
+__global__ void k_store_cursor_plan(const unsigned long long *__restrict__ peer_base, int nranks, unsigned long long cap,
+                                    uint32_t *status, CursorPlan *__restrict__ plan)
+{
+    const int d = threadIdx.x;
+    if (d <= MAX_SPLITTERS) {
+        plan->dest[d] = d < nranks ? peer_base[d] : 0ull;
+        plan->cursor[d] = d < nranks ? peer_base[d] + 4ull * cap : 0ull;
+    }
+    if (d == 0) {
+        plan->cap = (uint32_t)cap;
+        plan->unused = 0;
+        plan->status = status;
+    }
+}
+
+template <int THREADS, int KPT, int MINB, int LB, int RANK, class Binner, bool PTR_OUT, int UNORDERED = EXCH_ORDERED>
 __global__ void __launch_bounds__(THREADS, MINB)
     k_onesweep_bulk(const uint32_t *__restrict__ in, uint32_t *__restrict__ out, uint32_t n, const typename Binner::Arg binner_arg,
                     const void *__restrict__ base_v, uint32_t *__restrict__ base_next, uint32_t *__restrict__ desc,
@@ -139,6 +172,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
         // (3) bin threads: reduce over warps, publish the tile aggregate, finish the
         //     look-back, then lay the buckets out with the 16-byte phase of their destinations
         uint32_t my_count = 0, padded = 0, phase = 0, span4 = 0;
+        bool drop = false;  // EXCH_REMOTE_CURSOR: the destination is full, this run is not stored
         unsigned long long dst_addr = 0;  // byte address of the first destination of this tile's run
         if (tid < RADIX) {
 #pragma unroll
@@ -146,11 +180,20 @@ __global__ void __launch_bounds__(THREADS, MINB)
             my_count = padded;
             if ((uint32_t)tid == pad_bin) my_count -= (uint32_t)TILE - valid;  // padding keys carry the top digit
             uint32_t excl = 0;
-            if (UNORDERED) {
+            if (UNORDERED == EXCH_REMOTE_CURSOR) {
+                const CursorPlan *cp = static_cast<const CursorPlan *>(base_v);
+                if (my_count) {
+                    excl = atomicAdd_system(reinterpret_cast<uint32_t *>(cp->cursor[tid]), my_count);
+                    if (excl + my_count > cp->cap || excl + my_count < excl) {
+                        drop = true;
+                        atomicOr(cp->status, 1u);
+                    }
+                }
+            } else if (UNORDERED == EXCH_LOCAL_CURSOR) {
                 if (my_count) excl = atomicAdd(&desc[tid], my_count);
             } else
                 st_relaxed(&desc[(size_t)cur * RADIX + tid], (cur == 0 ? DESC_INCL : DESC_AGG) | my_count);
-            if (!UNORDERED && cur != 0) {
+            if (UNORDERED == EXCH_ORDERED && cur != 0) {
                 // windowed decoupled look-back: LB descriptors per round trip
                 uint32_t j = cur - 1;
                 bool done = false;
@@ -173,7 +216,9 @@ __global__ void __launch_bounds__(THREADS, MINB)
                 }
                 st_relaxed(&desc[(size_t)cur * RADIX + tid], DESC_INCL | (excl + my_count));
             }
-            if (PTR_OUT) {
+            if (PTR_OUT && UNORDERED == EXCH_REMOTE_CURSOR) {
+                dst_addr = my_count ? static_cast<const CursorPlan *>(base_v)->dest[tid] + 4ull * excl : 0ull;
+            } else if (PTR_OUT) {
                 dst_addr = static_cast<const unsigned long long *>(base_v)[tid] + 4ull * excl;
             } else {
                 const uint32_t gbase = static_cast<const uint32_t *>(base_v)[tid];
@@ -239,7 +284,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
         // (5) write-out: thread d owns bucket d.  Head and tail (the keys outside whole
         //     16-byte chunks of the destination) are stored one by one, the body goes to
         //     the bulk-copy engine.
-        if (tid < RADIX && my_count) {
+        if (tid < RADIX && my_count && !drop) {
             const uint32_t *src = reinterpret_cast<const uint32_t *>(tile_bytes + start4);
             uint32_t *dst = reinterpret_cast<uint32_t *>(dst_addr);
             const uint32_t head = min(my_count, (4u - phase) & 3u);

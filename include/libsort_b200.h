@@ -105,6 +105,22 @@ LIBSORT_API int libsortDeviceExchangePlanned(const uint32_t *d_in, size_t n, con
                                              const unsigned long long *d_peer_bases, size_t cap, uint32_t *d_nrecv,
                                              uint32_t *d_status, void *d_workspace, size_t workspace_bytes,
                                              void *stream);
+/*
+ * libsortDeviceExchangeCursor: the exchange with NO plan at all (DistributedSorter plan="cursor"; faster
+ *     than the counted layout at 2 GPUs, slower from 4 on: the atomics on one word per destination
+ *     serialise, see profiles/r02b_exchange_plan_ab.log).  Every rank's receive buffer holds `cap` keys followed by one cursor word (key
+ *     index cap; allocate at least (cap + 16) * 4 bytes), zero when the exchange starts on any rank.
+ *     d_peer_bases[r] = rank r's buffer as mapped on this GPU (DEVICE array of nranks addresses, own
+ *     buffer included).  Each tile reserves room for its run at destination r with one system-scope
+ *     atomicAdd on r's cursor over NVLink and bulk-copies the run there: no counting pass, no count
+ *     exchange, arrival order arbitrary.  Once every rank's exchange has completed (barrier), the
+ *     cursor word IS the number of keys received -- pass its address to libsortDeviceSortDyn as d_n.
+ *     A reservation that would pass cap is dropped and raises *d_status (sticky; zero it beforehand);
+ *     the destination's cursor then exceeds cap (libsortDeviceSortDyn clamps to its capacity).
+ */
+LIBSORT_API int libsortDeviceExchangeCursor(const uint32_t *d_in, size_t n, const uint32_t *splitters, int nranks,
+                                            const unsigned long long *d_peer_bases, size_t cap, uint32_t *d_status,
+                                            void *d_workspace, size_t workspace_bytes, void *stream);
 LIBSORT_API int libsortDeviceSortDyn(const uint32_t *d_in, uint32_t *d_out, uint32_t *d_tmp, size_t capacity,
                                      const uint32_t *d_n, void *d_workspace, size_t workspace_bytes, void *stream,
                                      LibsortKernelTimes *times);

@@ -11,10 +11,12 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 WORKER = os.path.join(ROOT, "tests", "dist_worker.py")
 
 
-def torchrun(nproc, port, *args, timeout=300):
+def torchrun(nproc, port, *args, timeout=300, env=None):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nproc),
            "--master-addr", "127.0.0.1", "--master-port", str(port), WORKER] + [str(a) for a in args]
-    return subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, cwd=ROOT)
+    e = dict(os.environ)
+    e.update(env or {})
+    return subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, cwd=ROOT, env=e)
 
 
 def test_plan_functions(pkg):
@@ -63,13 +65,15 @@ def test_plan_over_gloo(world):
 
 
 @pytest.mark.gpu
-def test_distributed_sort_on_gpus():
+@pytest.mark.parametrize("plan", ["counts", "cursor"])
+def test_distributed_sort_on_gpus(plan):
+    """Both receive-layout plans of the NVLink exchange (counted on the device / remote cursor atomics)."""
     import torch
     ndev = torch.cuda.device_count()
     if ndev < 2:
         pytest.skip("needs >= 2 GPUs")
     world = 2 if ndev < 4 else 4
-    r = torchrun(world, 29741, "nccl", 300000, timeout=600)
+    r = torchrun(world, 29741 if plan == "counts" else 29743, "nccl", 300000, timeout=600, env={"LIBSORT_EXCHANGE_PLAN": plan})
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
     assert r.stdout.count(" ok; keys/rank") == 10
     assert r.stdout.count("stepwise") == 3

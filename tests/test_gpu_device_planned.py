@@ -138,3 +138,82 @@ def test_planned_exchange_overflow_sets_status(gpu_lib, oracle):
     torch.cuda.synchronize()
     assert int(status.item()) == 1 and int(nrecv.item()) == 0
     assert bool((recv == -1).all())                        # nothing stored
+
+
+@pytest.mark.parametrize("W", [1, 2, 4, 8, 16])
+def test_cursor_exchange_virtual_ranks(gpu_lib, oracle, W):
+    """libsortDeviceExchangeCursor, W virtual ranks on one GPU: no counts anywhere -- every tile reserves
+    its room with an atomicAdd on the destination's cursor word (behind the `cap` keys of each receive
+    region).  Afterwards cursor r = keys of range r, the regions hold exactly those keys (any order)."""
+    import torch
+    L = gpu_lib
+    n = 70001 + 13 * W
+    stream = oracle.pcg_stream(n * W)
+    shards = [stream[r * n:(r + 1) * n].copy() for r in range(W)]
+    for s in shards:
+        s[::5] &= np.uint32(0x3FFFFFFF)
+    allk = np.sort(np.concatenate(shards))
+    spl = np.zeros(32, np.uint32)
+    for r in range(W - 1):
+        spl[r] = allk[(r + 1) * allk.size // W]
+    d_spl = torch.from_numpy(spl.view(np.int32)).cuda()
+    cap = int(n * 2 + 1024)
+    recv = torch.full((W, cap + 16), -1, dtype=torch.int32, device="cuda")
+    recv[:, cap:] = 0                                              # the cursor words
+    bases = torch.tensor([recv[r].data_ptr() for r in range(W)], dtype=torch.int64, device="cuda")
+    ws = torch.empty(max(L.libsortWorkspaceBytes(n), 1 << 20), dtype=torch.uint8, device="cuda")
+    status = torch.zeros(1, dtype=torch.int32, device="cuda")
+    for r in range(W):
+        k = torch.from_numpy(shards[r].view(np.int32)).cuda()
+        assert L.libsortDeviceExchangeCursor(k.data_ptr(), n, d_spl.data_ptr(), W, bases.data_ptr(), cap, status.data_ptr(),
+                                             ws.data_ptr(), ws.numel(), None) == 0
+    torch.cuda.synchronize()
+    assert int(status.item()) == 0
+    h = recv.cpu().numpy().view(np.uint32)
+    got_n = h[:, cap].astype(np.int64)
+    assert int(got_n.sum()) == n * W
+    for r in range(W):
+        assert np.all(h[r, got_n[r]:cap] == 0xFFFFFFFF)           # nothing beyond the cursor
+    parts = [np.sort(h[r, :got_n[r]]) for r in range(W)]
+    for a, b in zip(parts[:-1], parts[1:]):
+        if a.size and b.size:
+            assert a[-1] <= b[0]
+    assert np.array_equal(np.concatenate(parts), allk)
+    # the cursor word is the device-side key count of the local sort
+    dev_out = torch.empty(cap, dtype=torch.int32, device="cuda")
+    dev_tmp = torch.empty(cap, dtype=torch.int32, device="cuda")
+    ws2 = torch.empty(L.libsortWorkspaceBytes(cap), dtype=torch.uint8, device="cuda")
+    for r in range(W):
+        assert L.libsortDeviceSortDyn(recv[r].data_ptr(), dev_out.data_ptr(), dev_tmp.data_ptr(), cap,
+                                      recv[r][cap:].data_ptr(), ws2.data_ptr(), ws2.numel(), None, None) == 0
+        assert np.array_equal(dev_out[:got_n[r]].cpu().numpy().view(np.uint32), parts[r])
+
+
+def test_cursor_exchange_overflow(gpu_lib, oracle):
+    """A destination that would overflow: status raised, nothing written past cap, cursor > cap, and the
+    dynamic sort clamps to its capacity instead of running off the buffer."""
+    import torch
+    L = gpu_lib
+    n = 50000
+    k = oracle.pcg_stream(n)
+    d_k = torch.from_numpy(k.view(np.int32)).cuda()
+    d_spl = torch.zeros(32, dtype=torch.int32, device="cuda")
+    cap = 30000                                                    # a multiple of 4
+    recv = torch.full((cap + 16 + 4096,), -1, dtype=torch.int32, device="cuda")
+    recv[cap:cap + 16] = 0
+    bases = torch.tensor([recv.data_ptr()], dtype=torch.int64, device="cuda")
+    ws = torch.empty(max(L.libsortWorkspaceBytes(n), 1 << 20), dtype=torch.uint8, device="cuda")
+    status = torch.zeros(1, dtype=torch.int32, device="cuda")
+    assert L.libsortDeviceExchangeCursor(d_k.data_ptr(), n, d_spl.data_ptr(), 1, bases.data_ptr(), cap, status.data_ptr(),
+                                         ws.data_ptr(), ws.numel(), None) == 0
+    torch.cuda.synchronize()
+    assert int(status.item()) == 1
+    h = recv.cpu().numpy().view(np.uint32)
+    assert int(h[cap]) == n                                        # every reservation was counted
+    assert np.all(h[cap + 16:] == 0xFFFFFFFF)                      # nothing stored behind the buffer
+    out = torch.empty(cap, dtype=torch.int32, device="cuda")
+    tmp = torch.empty(cap, dtype=torch.int32, device="cuda")
+    ws2 = torch.empty(L.libsortWorkspaceBytes(cap), dtype=torch.uint8, device="cuda")
+    assert L.libsortDeviceSortDyn(recv.data_ptr(), out.data_ptr(), tmp.data_ptr(), cap, recv[cap:].data_ptr(),
+                                  ws2.data_ptr(), ws2.numel(), None, None) == 0
+    torch.cuda.synchronize()                                       # memory-safe: clamped to cap keys

@@ -1,11 +1,17 @@
 #!/bin/bash
-# usage: gpu_multi_ab.sh N v_a v_b ... -- distributed bench (uniform) once per build variant under build/
-N=${1:-2}; shift
+# usage: gpu_multi_ab.sh N [dists] -- exchange plan A/B at N GPUs: remote cursors (default) vs counted layout
+N=${1:-2}
+DISTS=${2:-uniform}
 mkdir -p gpurun_out
-for v in "$@"; do
-LIBSORT_SO=$PWD/build/$v/libsort.so timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29514 bench.py --gpus $N --steps 10 --warmup 3 > gpurun_out/bench_${N}gpu_$v.json 2> gpurun_out/bench_${N}gpu_$v.err
-grep -h '^{' gpurun_out/bench_${N}gpu_$v.json | python -c "
-import json,sys
-for l in sys.stdin:
-    j=json.loads(l); print('$v', round(j['value'],1),'Gkeys/s', round(j['ms_per_step'],2),'ms', {k: round(x,3) for k,x in j['phases_ms'].items() if x is not None}, j['verify']['ok'])" || tail -3 gpurun_out/bench_${N}gpu_$v.err
+for plan in cursor counts; do
+for d in $DISTS; do
+LIBSORT_EXCHANGE_PLAN=$plan timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus $N --steps 10 --warmup 3 --dist $d --quick > gpurun_out/ab_${N}gpu_${d}_$plan.json 2> gpurun_out/ab_${N}gpu_${d}_$plan.err
+python - <<PY
+import json
+try:
+    l=json.loads(open("gpurun_out/ab_${N}gpu_${d}_$plan.json").read().strip().splitlines()[-1])
+    print("$plan $d", round(l["value"],1), round(l["ms_per_step"],3), {k:round(v,3) for k,v in l["phases_ms"].items() if k.endswith("_ms")}, l["verify"]["ok"], round(l["verify"]["imbalance"],4))
+except Exception as e: print("no line", e)
+PY
+done
 done
