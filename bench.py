@@ -483,6 +483,7 @@ def multi_extras(args, rank, world, sorter, distrib, torch, dist, np):
     for d in ("zipf", "consthigh", "consthigh16", "allequal"):
         try:
             k = distrib.shard_of_pcg_stream(rank, n5, d)
+            sorter.reset_plan()
             for _ in range(2):
                 sorter.sort(k)
             torch.cuda.synchronize()
@@ -499,18 +500,20 @@ def multi_extras(args, rank, world, sorter, distrib, torch, dist, np):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             st = sorter.verify(k, out[:cnt], cnt)
             rows[d] = {"keys_total": n5 * world, "ms_per_step": float(t), "gkeys_s": n5 * world / float(t) / 1e6,
-                       "imbalance": st["imbalance"], "verified": st["ok"]}
+                       "imbalance": st["imbalance"], "verified": st["ok"], "plan": sorter.plan}
             del k
         except Exception as e:  # noqa: BLE001
             rows[d] = {"error": repr(e)}
     ex["c5_skew_1B"] = rows
     ex["c5_skew_1B"]["keys_total"] = n5 * world
     ns = 1 << 22
-    L = int(ns * 1.5) + (1 << 16)
+    L = ns * world          # a rank may end up with everything (first sort of a skewed input under plan="auto")
     exact = {}
     for d in ("uniform", "allequal", "consthigh"):
         try:
             k = distrib.shard_of_pcg_stream(rank, ns, d)
+            sorter.reset_plan()
+            sorter.sort(k)                      # plan="auto" settles on histogram or sampled splitters here
             out, cnt = sorter.sort(k)
             pad = torch.zeros(L, dtype=torch.int32, device="cuda")
             pad[:cnt] = out[:cnt]
@@ -540,7 +543,7 @@ def run_multi(args, rank, world, local_rank):
     distrib = importlib.import_module("gpu-radix-sort_b200.distrib")
     torch.cuda.set_device(local_rank)
     import datetime
-    dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank), timeout=datetime.timedelta(seconds=180))
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank), timeout=datetime.timedelta(seconds=90))
     n = args.keys
     # one continuous PCG stream; rank g owns elements [g*n, (g+1)*n)  
     clocks = ClockSampler(local_rank)
@@ -573,6 +576,7 @@ def run_multi(args, rank, world, local_rank):
     ms_local = torch.tensor([e0.elapsed_time(e1) / args.steps], device="cuda")
     dist.all_reduce(ms_local, op=dist.ReduceOp.MAX)
     ms = float(ms_local.item())
+    plan_used = sorter.plan if args.exchange == "p2p" else "host"
     stats = sorter.verify(d_in, out, cnt)           # sortedness, rank ordering, multiset fingerprint
     stats["rank_audit_violation"] = bool(getattr(sorter, "rank_violation", False))   # max over ranks (DistributedSorter._finish)
     phases = sorter.phase_times(d_in)               # per-phase CUDA-event times, max over ranks
@@ -594,6 +598,7 @@ def run_multi(args, rank, world, local_rank):
             "vs_baseline": None, "dtype": "u32", "data": "synthetic",
             "config": {"workload": "distributed uint32 sort, 2^28 keys per GPU (BASELINE configs[3] shape)",
                        "keys_per_gpu": n, "keys_total": total, "exchange": args.exchange, "distribution": args.dist,
+                       "exchange_plan": plan_used,
                        "parallelism": "key-range sharding, 1 rank/GPU, MSD bucketing + exchange + local LSD",
                        "l2": "1 GiB shard per step per GPU, larger than L2"},
             "clocks": clk, "verify": stats, "phases_ms": phases,

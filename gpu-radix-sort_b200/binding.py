@@ -15,7 +15,8 @@ ADDITIVE_SYMBOLS = ["libsortTileKeys", "libsortWorkspaceBytes", "libsortDeviceSo
                     "libsortIpcAlloc", "libsortIpcFree", "libsortIpcExport", "libsortIpcOpen", "libsortIpcClose", "libsortDistribSort",
                     "libsortStepTableBytes", "libsortStepTableInit", "libsortStepCounts", "libsortStepBases", "libsortStepScatter",
                     "libsortRankAudit", "libsortDeviceExchangePlanned", "libsortDeviceSortDyn",
-                    "libsortDebugLastDevice", "libsortDebugPoolOverlaps", "libsortDeviceExchangeCursor"]
+                    "libsortDebugLastDevice", "libsortDebugPoolOverlaps", "libsortDeviceExchangeCursor",
+                    "libsortDeviceTopHistogram", "libsortDeviceSplittersFromHistograms"]
 
 BOUNDS_REFERENCE = 0
 BOUNDS_EXACT = 1
@@ -107,6 +108,10 @@ def lib():
     L.libsortRankAudit.restype = ci
     L.libsortDeviceExchangePlanned.argtypes = [vp, sz, vp, ci, ci, vp, vp, sz, vp, vp, vp, sz, vp]
     L.libsortDeviceExchangePlanned.restype = ci
+    L.libsortDeviceTopHistogram.argtypes = [vp, sz, vp, vp]
+    L.libsortDeviceTopHistogram.restype = ci
+    L.libsortDeviceSplittersFromHistograms.argtypes = [vp, ci, vp, vp, vp, vp]
+    L.libsortDeviceSplittersFromHistograms.restype = ci
     L.libsortDeviceExchangeCursor.argtypes = [vp, sz, vp, ci, vp, sz, vp, vp, sz, vp]
     L.libsortDeviceExchangeCursor.restype = ci
     L.libsortDeviceSortDyn.argtypes = [vp, vp, vp, sz, vp, vp, sz, vp, ctypes.POINTER(KernelTimes)]

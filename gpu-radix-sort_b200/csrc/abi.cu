@@ -469,6 +469,17 @@ API int libsortDeviceExchangePlanned(const uint32_t *d_in, size_t n, const uint3
                                  d_workspace, workspace_len, (cudaStream_t)stream);
 }
 
+API int libsortDeviceTopHistogram(const uint32_t *d_in, size_t n, uint32_t *d_hist4096, void *stream)
+{
+    return (int)top_histogram(d_in, n, d_hist4096, (cudaStream_t)stream);
+}
+API int libsortDeviceSplittersFromHistograms(const uint32_t *d_all_hists, int nranks, uint32_t *d_splitters,
+                                             uint32_t *d_count_matrix, uint32_t *d_imbalance_permille, void *stream)
+{
+    return (int)splitters_from_histograms(d_all_hists, nranks, d_splitters, d_count_matrix, d_imbalance_permille,
+                                          (cudaStream_t)stream);
+}
+
 API int libsortDeviceExchangeCursor(const uint32_t *d_in, size_t n, const uint32_t *splitters, int nranks,
                                     const unsigned long long *d_peer_bases, size_t cap, uint32_t *d_status,
                                     void *d_workspace, size_t workspace_len, void *stream)

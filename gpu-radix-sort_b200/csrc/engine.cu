@@ -715,6 +715,28 @@ cudaError_t exchange_planned(const uint32_t *in, size_t n, const uint32_t *split
     return cudaGetLastError();
 }
 
+cudaError_t top_histogram(const uint32_t *in, size_t n, uint32_t *d_hist, cudaStream_t st)
+{
+    if (!d_hist || n >= (1ull << 32)) return cudaErrorInvalidValue;
+    DevInfo *dev = nullptr;
+    CK(dev_info(&dev));
+    CK(cudaMemsetAsync(d_hist, 0, TOP_BINS * sizeof(uint32_t), st));
+    if (n == 0) return cudaSuccess;
+    const size_t want = (n / 4 + 512 * 4 - 1) / (512 * 4);
+    const int grid = (int)std::max<size_t>(1, std::min<size_t>((size_t)dev->sms * 4, want));
+    k_hist_top12<512><<<grid, 512, 0, st>>>(in, n, d_hist);
+    return cudaGetLastError();
+}
+
+cudaError_t splitters_from_histograms(const uint32_t *d_all_hists, int nranks, uint32_t *d_splitters, uint32_t *d_count_matrix,
+                                      uint32_t *d_imbalance_permille, cudaStream_t st)
+{
+    if (nranks < 1 || nranks > MAX_SPLITTERS + 1 || !d_all_hists || !d_splitters || !d_count_matrix || !d_imbalance_permille)
+        return cudaErrorInvalidValue;
+    k_splitters_from_hist<<<1, 1024, 0, st>>>(d_all_hists, nranks, d_splitters, d_count_matrix, d_imbalance_permille);
+    return cudaGetLastError();
+}
+
 cudaError_t exchange_cursor(const uint32_t *in, size_t n, const uint32_t *splitters, int nranks,
                             const unsigned long long *d_peer_bases, size_t cap, uint32_t *d_status, void *workspace,
                             size_t workspace_len, cudaStream_t st)

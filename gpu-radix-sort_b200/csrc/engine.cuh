@@ -95,6 +95,15 @@ cudaError_t exchange_planned(const uint32_t *in, size_t n, const uint32_t *split
                              uint32_t *d_nrecv, uint32_t *d_status, void *workspace, size_t workspace_len,
                              cudaStream_t st);
 
+// Splitters and the count matrix from histograms instead of a sample + counting pass (kernels.cuh
+// "splitters straight from a histogram"): top_histogram = 4096 bins of key >> 20 of one shard (zeroes
+// d_hist first); splitters_from_histograms = the all-gathered nranks x 4096 histograms -> 32-word splitter
+// table, nranks x 16 count matrix (the layout exchange_planned takes) and the imbalance those
+// bin-aligned splitters give (largest range * 1000 / mean).
+cudaError_t top_histogram(const uint32_t *in, size_t n, uint32_t *d_hist, cudaStream_t st);
+cudaError_t splitters_from_histograms(const uint32_t *d_all_hists, int nranks, uint32_t *d_splitters, uint32_t *d_count_matrix,
+                                      uint32_t *d_imbalance_permille, cudaStream_t st);
+
 // The exchange without any plan: every receive buffer is followed by its cursor word (at key index
 // `cap`), zero before the exchange; sources reserve room for each tile's run with a system-scope
 // atomicAdd on the destination's cursor (NVLink), so no rank needs to know any counts beforehand.

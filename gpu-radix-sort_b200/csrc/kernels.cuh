@@ -920,6 +920,151 @@ __global__ void k_plan_exchange(const uint32_t *__restrict__ cm, int nranks, int
     }
 }
 
+// ---- splitters straight from a histogram (distributed sort, plan = "hist") -------------------
+// For inputs whose top 12 bits are spread well enough, neither a sample nor a counting pass is
+// needed: one 4096-bin histogram of key >> 20 per shard (k_hist_top12, one read of the shard),
+// all-gathered, gives (a) splitters on bin boundaries that cut the union into nranks near-equal
+// ranges and (b) the exact nranks x nranks count matrix for those splitters -- what the sample sort
+// + k_dest_hist pass + count all-gather produce otherwise.  k_splitters_from_hist also reports the
+// resulting imbalance (largest range * 1000 / mean) so that the host side can fall back to sampled
+// splitters with tie thresholds for inputs this cannot balance (few distinct top bits, heavy ties).
+constexpr int TOP_BITS = 12, TOP_BINS = 1 << TOP_BITS, TOP_SHIFT = 32 - TOP_BITS;
+
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS) k_hist_top12(const uint32_t *__restrict__ in, size_t n, uint32_t *__restrict__ ghist)
+{
+    __shared__ uint32_t s_hist[TOP_BINS];
+    for (int i = threadIdx.x; i < TOP_BINS; i += THREADS) s_hist[i] = 0;
+    __syncthreads();
+    auto count = [&](uint32_t k) { atomicAdd(&s_hist[k >> TOP_SHIFT], 1u); };
+    size_t head = ((16u - (reinterpret_cast<uintptr_t>(in) & 15u)) & 15u) >> 2;
+    if (head > n) head = n;
+    const size_t nvec = (n - head) >> 2, tail0 = head + (nvec << 2);
+    const size_t gtid = (size_t)blockIdx.x * THREADS + threadIdx.x, gstride = (size_t)gridDim.x * THREADS;
+    if (gtid < head) count(in[gtid]);
+    if (gtid < n - tail0) count(in[tail0 + gtid]);
+    const uint4 *vin = reinterpret_cast<const uint4 *>(in + head);
+    constexpr int U = 4;
+    size_t i = gtid;
+    for (; i + (U - 1) * gstride < nvec; i += U * gstride) {
+        uint4 v[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) v[u] = ld_stream_v4(vin + i + u * gstride);
+#pragma unroll
+        for (int u = 0; u < U; u++) { count(v[u].x); count(v[u].y); count(v[u].z); count(v[u].w); }
+    }
+    for (; i < nvec; i += gstride) {
+        const uint4 v = ld_stream_v4(vin + i);
+        count(v.x); count(v.y); count(v.z); count(v.w);
+    }
+    __syncthreads();
+    for (int j = threadIdx.x; j < TOP_BINS; j += THREADS) {
+        const uint32_t c = s_hist[j];
+        if (c) atomicAdd(&ghist[j], c);
+    }
+}
+
+// One CTA of 1024 threads, 4 bins each.  hists: nranks x 4096 (all-gathered).  Writes the 32-word
+// splitter table (values on bin boundaries, tie thresholds 0), the count matrix in the layout of the
+// all-gathered k_dest_hist counts (nranks x 16) and *imbalance_permille.
+__global__ void __launch_bounds__(1024) k_splitters_from_hist(const uint32_t *__restrict__ hists, int nranks,
+                                                              uint32_t *__restrict__ splitters, uint32_t *__restrict__ cm,
+                                                              uint32_t *__restrict__ imbalance_permille)
+{
+    __shared__ unsigned long long s_warp[32];
+    __shared__ uint32_t s_e[MAX_SPLITTERS + 2];
+    __shared__ unsigned long long s_cm[MAX_SPLITTERS + 1][MAX_SPLITTERS + 1];
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    uint32_t cnt[4];
+    unsigned long long mine = 0;
+    cnt[0] = cnt[1] = cnt[2] = cnt[3] = 0;  // a bin of the union holds < 2^32 keys (shards are < 2^28 keys in practice)
+    for (int r = 0; r < nranks; r++) {
+        const uint4 h = *reinterpret_cast<const uint4 *>(hists + (size_t)r * TOP_BINS + 4 * t);
+        cnt[0] += h.x; cnt[1] += h.y; cnt[2] += h.z; cnt[3] += h.w;
+    }
+    mine = (unsigned long long)cnt[0] + cnt[1] + cnt[2] + cnt[3];
+    if (t < (MAX_SPLITTERS + 1) * (MAX_SPLITTERS + 1)) (&s_cm[0][0])[t] = 0;
+    if (t < MAX_SPLITTERS + 2) s_e[t] = 0;
+    // block exclusive scan of `mine`
+    unsigned long long inc = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned long long v = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += v;
+    }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    unsigned long long wbase = 0, total = 0;
+    for (int w = 0; w < 32; w++) {
+        const unsigned long long c = s_warp[w];
+        if (w < warp) wbase += c;
+        total += c;
+    }
+    unsigned long long excl = wbase + inc - mine;
+    __shared__ unsigned long long s_target[MAX_SPLITTERS + 1];
+    if (t >= 1 && t < nranks) s_target[t] = total * (unsigned long long)t / (unsigned long long)nranks;
+    __syncthreads();
+    // boundary g (between rank g-1 and g) = the bin edge closest to the g/nranks quantile
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const uint32_t b = 4 * t + k;
+        if (cnt[k]) {
+            for (int g = 1; g < nranks; g++) {
+                const unsigned long long target = s_target[g];
+                if (excl <= target && target < excl + cnt[k]) {
+                    uint32_t e = (target - excl <= cnt[k] / 2) ? b : b + 1;
+                    s_e[g] = min(e, (uint32_t)TOP_BINS - 1u);  // the last bin always stays right of every splitter
+                }
+            }
+        }
+        excl += cnt[k];
+    }
+    if (t == 0) s_e[nranks] = TOP_BINS;
+    __syncthreads();
+    // count matrix for those boundaries: destinations are monotone in the bin index, so a warp (128
+    // consecutive bins) meets only a few of them -- reduce inside the warp, one atomic per (warp, source, destination)
+    int dk[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        int d = 0;
+        for (int g = 1; g < nranks; g++) d += s_e[g] <= (uint32_t)(4 * t + k) ? 1 : 0;
+        dk[k] = d;
+    }
+    const int dlo = __shfl_sync(0xffffffffu, dk[0], 0), dhi = __shfl_sync(0xffffffffu, dk[3], 31);
+    for (int r = 0; r < nranks; r++) {
+        const uint4 h = *reinterpret_cast<const uint4 *>(hists + (size_t)r * TOP_BINS + 4 * t);
+        const uint32_t hv[4] = {h.x, h.y, h.z, h.w};
+        for (int d = dlo; d <= dhi; d++) {
+            uint32_t v = 0;
+#pragma unroll
+            for (int k = 0; k < 4; k++) v += dk[k] == d ? hv[k] : 0u;
+            unsigned long long sum = v;  // <= 128 bins of < 2^30 keys each
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+            if (lane == 0 && sum) atomicAdd(&s_cm[r][d], sum);
+        }
+    }
+    __syncthreads();
+    if (t < (MAX_SPLITTERS + 1) * (MAX_SPLITTERS + 1)) {
+        const int r = t / (MAX_SPLITTERS + 1), d = t % (MAX_SPLITTERS + 1);
+        if (r < nranks) cm[r * (MAX_SPLITTERS + 1) + d] = (uint32_t)min(s_cm[r][d], 0xffffffffull);
+    }
+    if (t < 2 * (MAX_SPLITTERS + 1)) {
+        uint32_t v = 0;
+        if (t < nranks - 1) v = s_e[t + 1] << TOP_SHIFT;
+        splitters[t] = v;  // [0,16): values, [16,32): tie thresholds (none)
+    }
+    if (t == 0) {
+        unsigned long long worst = 0;
+        for (int d = 0; d < nranks; d++) {
+            unsigned long long tot = 0;
+            for (int r = 0; r < nranks; r++) tot += s_cm[r][d];
+            worst = max(worst, tot);
+        }
+        *imbalance_permille = total ? (uint32_t)min(worst * 1000ull * (unsigned long long)nranks / total, 0xffffffffull) : 1000u;
+    }
+}
+
 // ------------------------------------------------------------ boundaries --
 // Exact boundaries for wide groups: thread g finds the first index whose
 // group is >= g in the array already sorted by those bits.

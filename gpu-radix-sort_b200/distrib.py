@@ -48,6 +48,7 @@ from . import binding, distrib_plan
 from .binding import KernelTimes
 
 SAMPLES_PER_RANK = 1 << 13   # 8 K per rank: the quantiles of P x 8 K samples balance to about 1 %
+HIST_IMBALANCE_LIMIT = 1.03  # plan="auto": above this the histogram plan gives way to sampled splitters
 
 
 def _u32_to_i32(v64):
@@ -94,9 +95,13 @@ class DistributedSorter:
         if mode not in ("p2p", "nccl"):
             raise ValueError(mode)
         self.mode = mode
-        self.plan = plan or os.environ.get("LIBSORT_EXCHANGE_PLAN", "counts")
-        if self.plan not in ("cursor", "counts"):
-            raise ValueError(self.plan)
+        # "auto" (default): splitters and counts from one 4096-bin histogram per shard (plan "hist") as
+        # long as that balances the ranks to within HIST_IMBALANCE_LIMIT; otherwise, from the next sort
+        # on, sampled splitters with tie thresholds + a counting pass ("counts").  "cursor": see above.
+        self.plan_arg = plan or os.environ.get("LIBSORT_EXCHANGE_PLAN", "auto")
+        if self.plan_arg not in ("auto", "hist", "cursor", "counts"):
+            raise ValueError(self.plan_arg)
+        self.plan = "hist" if self.plan_arg == "auto" else self.plan_arg
         self.lib = binding.lib()
         self.dev = torch.device("cuda", torch.cuda.current_device())
         self.n_max = n_local_max
@@ -145,6 +150,9 @@ class DistributedSorter:
         self.token = torch.zeros(1, dtype=i32, device=dev)
         self.h_counts = torch.empty(16 * self.world, dtype=i32).pin_memory()
         self.d_peer_bases = torch.tensor(self.peer_ptrs, dtype=torch.int64, device=dev)
+        self.top_hist = torch.zeros(4096, dtype=i32, device=dev)
+        self.all_top_hists = torch.zeros(4096 * self.world, dtype=i32, device=dev)
+        self.d_imbalance = torch.full((1,), 1000, dtype=i32, device=dev)
         self.d_nrecv = torch.zeros(1, dtype=i32, device=dev)
         self.d_status = torch.zeros(1, dtype=i32, device=dev)
         self.seed = 1
@@ -152,11 +160,24 @@ class DistributedSorter:
         # kernels per sort: sample, sample sort (hist, scan, 4 passes), pick, dest hist, store ptrs,
         # scatter, local sort (hist, scan, 4 passes)
         # p2p: sample, sample sort (hist, scan, 4 passes), pick, dest hist, plan, scatter, local sort (hist, scan, 4 passes)
-        # p2p, plan="cursor": sample, sample sort (6), pick, store plan, scatter, local sort (6)
-        self.launches_per_sort = (1 + 6 + 1 + 1 + 1 + 6) if (mode == "p2p" and self.plan == "cursor") else (1 + 6 + 1 + 1 + 1 + 1 + 6)
         self.launches_per_stepwise_sort = 4 * 3    # per step: histogram, bases, scatter
         self.last_totals = None
         self.rank_violation = False
+        self.hist_imbalance = None
+
+    @property
+    def launches_per_sort(self):
+        """Kernels of ours per sort in the current plan (bench.py's gpu_launches)."""
+        local = 6                                   # histogram, scan, 4 scatter passes
+        if self.mode != "p2p" or self.plan == "counts":
+            return 1 + 6 + 1 + 1 + 1 + 1 + local    # sample, sample sort, pick, dest hist, plan / store ptrs, scatter
+        if self.plan == "cursor":
+            return 1 + 6 + 1 + 1 + 1 + local        # sample, sample sort, pick, store plan, scatter
+        return 1 + 1 + 1 + 1 + local                # top histogram, splitters from histograms, plan, scatter
+
+    def reset_plan(self):
+        """plan="auto": forget that an earlier input needed sampled splitters (new data, new try)."""
+        self.plan = "hist" if self.plan_arg == "auto" else self.plan_arg
 
     def close(self):
         if self._step is not None:
@@ -229,7 +250,10 @@ class DistributedSorter:
             raise ValueError("shard larger than the sorter was built for")
         if self.plan == "cursor":
             return self._sort_async_cursor(keys, ev, times)
-        self._plan(keys, ev, on_host=False)
+        if self.plan == "hist":
+            self._plan_from_histograms(keys, ev)
+        else:
+            self._plan(keys, ev, on_host=False)
         binding.check(L.libsortDeviceExchangePlanned(keys.data_ptr(), n, self.splitters.data_ptr(), W, me,
                                                      self.count_matrix.data_ptr(), self.d_peer_bases.data_ptr(), self.cap,
                                                      self.d_nrecv.data_ptr(), self.d_status.data_ptr(),
@@ -248,6 +272,24 @@ class DistributedSorter:
         if ev:
             ev("local_sort")
         return self.out, self.d_nrecv
+
+    def _plan_from_histograms(self, keys, ev=None):
+        """plan="hist": one read of the shard (4096-bin histogram of the top 12 bits), one all-gather,
+        one small kernel -> splitters on bin boundaries + the exact count matrix.  No sample, no sample
+        sort, no counting pass."""
+        L, st, n, W = self.lib, self._stream(), keys.numel(), self.world
+        binding.check(L.libsortDeviceTopHistogram(keys.data_ptr(), n, self.top_hist.data_ptr(), st), "top histogram")
+        if W > 1:
+            dist.all_gather_into_tensor(self.all_top_hists, self.top_hist, group=self.group)
+        else:
+            self.all_top_hists.copy_(self.top_hist)
+        if ev:
+            ev("splitters")
+        binding.check(L.libsortDeviceSplittersFromHistograms(self.all_top_hists.data_ptr(), W, self.splitters.data_ptr(),
+                                                             self.count_matrix.data_ptr(), self.d_imbalance.data_ptr(), st),
+                      "splitters from histograms")
+        if ev:
+            ev("counts")
 
     def _sort_async_cursor(self, keys, ev, times):
         """splitters -> exchange with remote cursors -> local sort on the cursor's value.  No counting
@@ -284,6 +326,13 @@ class DistributedSorter:
         rc = self.lib.libsortRankAudit(self._stream())
         if rc < 0:
             binding.check(rc, "libsortRankAudit")
+        switched = False
+        if self.plan == "hist" and self.plan_arg == "auto":
+            # every rank computed the same figure from the same gathered histograms: no collective needed
+            self.hist_imbalance = int(self.d_imbalance.item()) / 1000.0
+            if self.hist_imbalance > HIST_IMBALANCE_LIMIT:
+                self.plan = "counts"        # bin-aligned splitters cannot balance this input: sample from now on
+                switched = True
         mine = torch.stack([self.d_nrecv[0], self.d_status[0], torch.tensor(rc, dtype=torch.int32, device=self.dev)])
         if W > 1:
             allv = torch.empty(3 * W, dtype=torch.int32, device=self.dev)
@@ -295,6 +344,8 @@ class DistributedSorter:
         nrecv = int(v[self.rank, 0])
         if v[:, 1].any() or int(v[:, 0].max()) > self.cap:
             self.d_status.zero_()
+            if switched:
+                return -1               # overflow under bin-aligned splitters: sort() repeats with sampled ones
             raise RuntimeError("receive buffer too small: %d keys arrive at one rank, capacity %d (raise slack)"
                                % (int(v[:, 0].max()), self.cap))
         self.rank_violation = bool(v[:, 2].any())
@@ -308,11 +359,16 @@ class DistributedSorter:
         if n > self.n_max:
             raise ValueError("shard larger than the sorter was built for")
         if self.mode == "p2p":
-            for _attempt in range(2):       # `keys` is untouched: after a ranking violation sort it again (ballot kernels)
+            # `keys` is untouched, so the sort can simply be repeated: after a ranking violation (ballot
+            # kernels from then on) or when the histogram plan overflowed a receive buffer (sampled
+            # splitters from then on)
+            for _attempt in range(3):
                 out, _ = self.sort_async(keys, ev=ev, times=times)
                 nrecv = self._finish()
-                if not self.rank_violation:
+                if nrecv >= 0 and not self.rank_violation:
                     break
+            if nrecv < 0:
+                raise RuntimeError("receive buffer too small (raise slack)")
             return out[:nrecv], nrecv
         cm = self._plan(keys, ev)
         offsets, totals = distrib_plan.recv_layout(cm)

@@ -106,6 +106,20 @@ LIBSORT_API int libsortDeviceExchangePlanned(const uint32_t *d_in, size_t n, con
                                              uint32_t *d_status, void *d_workspace, size_t workspace_bytes,
                                              void *stream);
 /*
+ * Splitters without a sample and without a counting pass (DistributedSorter plan="hist"):
+ * libsortDeviceTopHistogram: d_hist4096[b] = keys of the shard with key >> 20 == b (zeroed first).
+ * libsortDeviceSplittersFromHistograms: from the all-gathered nranks x 4096 histograms (DEVICE) ->
+ *     the 32-word splitter table (splitters on bin boundaries, no tie thresholds), the nranks x 16
+ *     count matrix in the layout libsortDeviceExchangePlanned takes, and *d_imbalance_permille =
+ *     largest range * 1000 / mean under those splitters.  Exact for any input; balanced only when
+ *     the keys spread over enough of the 4096 top-bit bins -- callers fall back to sampled splitters
+ *     (libsortDeviceSample / PickSplitters / SplitCounts) when the imbalance is too high.
+ */
+LIBSORT_API int libsortDeviceTopHistogram(const uint32_t *d_in, size_t n, uint32_t *d_hist4096, void *stream);
+LIBSORT_API int libsortDeviceSplittersFromHistograms(const uint32_t *d_all_hists, int nranks, uint32_t *d_splitters,
+                                                     uint32_t *d_count_matrix, uint32_t *d_imbalance_permille,
+                                                     void *stream);
+/*
  * libsortDeviceExchangeCursor: the exchange with NO plan at all (DistributedSorter plan="cursor"; faster
  *     than the counted layout at 2 GPUs, slower from 4 on: the atomics on one word per destination
  *     serialise, see profiles/r02b_exchange_plan_ab.log).  Every rank's receive buffer holds `cap` keys followed by one cursor word (key

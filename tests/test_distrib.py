@@ -65,15 +65,16 @@ def test_plan_over_gloo(world):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("plan", ["counts", "cursor"])
+@pytest.mark.parametrize("plan", ["auto", "counts", "cursor"])
 def test_distributed_sort_on_gpus(plan):
-    """Both receive-layout plans of the NVLink exchange (counted on the device / remote cursor atomics)."""
+    """Every plan of the NVLink exchange: histogram splitters with automatic fall-back to sampled ones,
+    sampled splitters + counted layout, remote cursor atomics."""
     import torch
     ndev = torch.cuda.device_count()
     if ndev < 2:
         pytest.skip("needs >= 2 GPUs")
     world = 2 if ndev < 4 else 4
-    r = torchrun(world, 29741 if plan == "counts" else 29743, "nccl", 300000, timeout=600, env={"LIBSORT_EXCHANGE_PLAN": plan})
+    r = torchrun(world, {"auto": 29741, "counts": 29743, "cursor": 29745}[plan], "nccl", 300000, timeout=600, env={"LIBSORT_EXCHANGE_PLAN": plan})
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
     assert r.stdout.count(" ok; keys/rank") == 10
     assert r.stdout.count("stepwise") == 3

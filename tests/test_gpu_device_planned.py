@@ -217,3 +217,58 @@ def test_cursor_exchange_overflow(gpu_lib, oracle):
     assert L.libsortDeviceSortDyn(recv.data_ptr(), out.data_ptr(), tmp.data_ptr(), cap, recv[cap:].data_ptr(),
                                   ws2.data_ptr(), ws2.numel(), None, None) == 0
     torch.cuda.synchronize()                                       # memory-safe: clamped to cap keys
+
+
+@pytest.mark.parametrize("W,kind", [(1, "uniform"), (2, "uniform"), (8, "uniform"), (16, "uniform"), (4, "lowbits"), (8, "clustered")])
+def test_splitters_from_histograms(gpu_lib, oracle, W, kind):
+    """plan="hist": 4096-bin top-bit histograms -> bin-aligned splitters + the exact count matrix, then
+    the planned exchange with them (virtual ranks).  Checked against numpy on the same keys."""
+    import torch
+    L = gpu_lib
+    n = 60000 + 11 * W
+    stream = oracle.pcg_stream(n * W)
+    if kind == "lowbits":
+        stream = stream & np.uint32(0x000FFFFF)                    # one top-bit bin holds everything
+    elif kind == "clustered":
+        stream = (stream >> np.uint32(3)) + np.uint32(0x60000000)  # an eighth of the key space
+    shards = [stream[r * n:(r + 1) * n].copy() for r in range(W)]
+    d_keys = [torch.from_numpy(s.view(np.int32)).cuda() for s in shards]
+    hists = torch.zeros((W, 4096), dtype=torch.int32, device="cuda")
+    for r in range(W):
+        hists[r] = 77                                              # the call zeroes its output first
+        assert L.libsortDeviceTopHistogram(d_keys[r].data_ptr(), n, hists[r].data_ptr(), None) == 0
+    want_h = np.stack([np.bincount(s >> np.uint32(20), minlength=4096) for s in shards])
+    assert np.array_equal(hists.cpu().numpy(), want_h)
+    spl = torch.full((32,), -1, dtype=torch.int32, device="cuda")
+    cm = torch.zeros((W, 16), dtype=torch.int32, device="cuda")
+    imb = torch.zeros(1, dtype=torch.int32, device="cuda")
+    assert L.libsortDeviceSplittersFromHistograms(hists.data_ptr(), W, spl.data_ptr(), cm.data_ptr(), imb.data_ptr(), None) == 0
+    h_spl = spl.cpu().numpy().view(np.uint32)
+    s_val = h_spl[:W - 1].astype(np.uint64)
+    assert np.all(h_spl[16:] == 0) and np.all(s_val % (1 << 20) == 0) and np.all(np.diff(s_val.astype(np.int64)) >= 0)
+    want_cm = np.zeros((W, 16), np.int64)
+    for r in range(W):
+        dest = np.searchsorted(s_val, shards[r].astype(np.uint64), side="right")   # number of splitters <= key
+        want_cm[r, :W] = np.bincount(dest, minlength=W)
+    assert np.array_equal(cm.cpu().numpy().astype(np.int64), want_cm)
+    totals = want_cm.sum(axis=0)[:W]
+    assert int(imb.item()) == int(totals.max()) * 1000 * W // (n * W)
+    if kind == "uniform":
+        assert int(imb.item()) <= 1030                             # 4096 bins balance uniform keys
+    elif kind == "lowbits" and W > 1:
+        assert int(imb.item()) == 1000 * W                         # cannot be balanced: the caller falls back to sampling
+    # the planned exchange accepts table and matrix as they are
+    cap = n * W + 64
+    recv = torch.full((W, cap), -1, dtype=torch.int32, device="cuda")
+    bases = torch.tensor([recv[r].data_ptr() for r in range(W)], dtype=torch.int64, device="cuda")
+    ws = torch.empty(max(L.libsortWorkspaceBytes(n), 1 << 20), dtype=torch.uint8, device="cuda")
+    nrecv = torch.zeros(W, dtype=torch.int32, device="cuda")
+    status = torch.zeros(1, dtype=torch.int32, device="cuda")
+    for r in range(W):
+        assert L.libsortDeviceExchangePlanned(d_keys[r].data_ptr(), n, spl.data_ptr(), W, r, cm.data_ptr(), bases.data_ptr(),
+                                              cap, nrecv[r:].data_ptr(), status.data_ptr(), ws.data_ptr(), ws.numel(), None) == 0
+    torch.cuda.synchronize()
+    assert int(status.item()) == 0 and np.array_equal(nrecv.cpu().numpy().astype(np.int64), totals)
+    h = recv.cpu().numpy().view(np.uint32)
+    got = np.concatenate([np.sort(h[r, :totals[r]]) for r in range(W)])
+    assert np.array_equal(got, np.sort(np.concatenate(shards)))

@@ -3,7 +3,7 @@
 N=${1:-2}
 DISTS=${2:-uniform}
 mkdir -p gpurun_out
-for plan in cursor counts; do
+for plan in ${PLANS:-auto counts}; do
 for d in $DISTS; do
 LIBSORT_EXCHANGE_PLAN=$plan timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus $N --steps 10 --warmup 3 --dist $d --quick > gpurun_out/ab_${N}gpu_${d}_$plan.json 2> gpurun_out/ab_${N}gpu_${d}_$plan.err
 python - <<PY
