@@ -18,6 +18,7 @@ straight into a caller-provided buffer -- e.g. pinned memory that the GPU then D
 """
 import json
 import os
+import threading
 import pathlib
 import shutil
 
@@ -131,6 +132,14 @@ class fileDistribArray(DistribArray):
             json.dump({"Lens": self.shape.lens, "Caps": self.shape.caps}, f)
         self.closed = True
 
+    def Abandon(self):
+        """Drop the handle WITHOUT writing the metadata: for a handle whose files were destroyed or
+        replaced behind it (its lengths would overwrite the new array's meta.json)."""
+        if not self.closed:
+            os.close(self._fd)
+            self._fd = -1
+            self.closed = True
+
     def Destroy(self):
         if self._fd >= 0:
             os.close(self._fd)
@@ -208,23 +217,40 @@ class partRef:
         return self.arr.ReadPart(self.partID, start=self.start, nbyte=self.nbyte, dest=dest)
 
 
-# arrays opened on behalf of requests, by name: one descriptor per array however many slices name it
+# arrays opened on behalf of requests, by name: one descriptor per array however many slices name it.
+# Worker threads (faas.py) share the cache: every lookup and replacement happens under the lock.
 openArrs = {}
+_openArrsLock = threading.Lock()
 
 
 def closeOpenArrays():
     """Close every array opened through getPartRefs (the reference leaves them open for the process lifetime)."""
-    for arr in openArrs.values():
-        arr.Close()
-    openArrs.clear()
+    with _openArrsLock:
+        for arr in openArrs.values():
+            arr.Close()
+        openArrs.clear()
+
+
+def _still_the_same_file(arr):
+    """A cached handle is valid only while its descriptor is the file now at that path: an array that
+    was destroyed and re-created under the same name is another file (and possibly has new lengths)."""
+    try:
+        now, held = os.stat(arr.datPath), os.fstat(arr._fd)
+    except OSError:
+        return False
+    # st_nlink == 0: the held file was unlinked (its inode number may already belong to the new file)
+    return held.st_nlink > 0 and (now.st_ino, now.st_dev) == (held.st_ino, held.st_dev)
 
 
 def _file_ref(entry):
     name = entry["arrayName"]
-    arr = openArrs.get(name)
-    if arr is None or arr.closed or not arr.rootPath.exists() or arr.rootPath.parent != FileDistribArrayMount:
-        arr = fileDistribArray.Open(FileDistribArrayMount / name)
-        openArrs[name] = arr
+    with _openArrsLock:
+        arr = openArrs.get(name)
+        if (arr is None or arr.closed or arr.rootPath.parent != FileDistribArrayMount or not _still_the_same_file(arr)):
+            if arr is not None:
+                arr.Abandon()
+            arr = fileDistribArray.Open(FileDistribArrayMount / name)
+            openArrs[name] = arr
     nbyte = entry["nbyte"]
     if nbyte == -1:   # "the remainder of the partition (from start)", faasTest/README.md:52
         nbyte = arr.shape.lens[entry["partID"]] - entry["start"]

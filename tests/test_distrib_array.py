@@ -112,6 +112,31 @@ def test_part_refs_and_requests(da, tmp_path):
     da.closeOpenArrays()
 
 
+def test_request_cache_sees_recreated_arrays_and_is_thread_safe(da, tmp_path):
+    """getPartRefs caches one open handle per array name for the life of a worker: a name that is
+    destroyed and created again (new inode, new lengths) must not be served from the stale handle,
+    and concurrent requests share one handle instead of leaking descriptors."""
+    from concurrent.futures import ThreadPoolExecutor
+    da.SetDistribMount(tmp_path)
+    a = da.fileDistribArray.Create(tmp_path / "reused", da.ArrayShape.fromUniform(8, 1))
+    a.WritePart(0, b"AAAAAAAA")
+    a.Close()
+    req = {"offset": 0, "width": 2, "arrType": "file", "input": [{"arrayName": "reused", "partID": 0, "start": 0, "nbyte": -1}]}
+    assert da.getPartRefs(req)[0].read() == b"AAAAAAAA"
+    first = da.openArrs["reused"]
+    da.fileDistribArray.Open(tmp_path / "reused").Destroy()
+    b = da.fileDistribArray.Create(tmp_path / "reused", da.ArrayShape.fromUniform(12, 1))
+    b.WritePart(0, b"BBBBBBBBBBBB")
+    b.Close()
+    assert da.getPartRefs(req)[0].read() == b"BBBBBBBBBBBB"        # not the unlinked inode, not the old length
+    assert da.openArrs["reused"] is not first and first.closed
+    da.closeOpenArrays()
+    with ThreadPoolExecutor(8) as ex:
+        got = list(ex.map(lambda _: (da.getPartRefs(req)[0].read(), id(da.openArrs["reused"])), range(64)))
+    assert all(g[0] == b"BBBBBBBBBBBB" for g in got) and len({g[1] for g in got}) == 1
+    da.closeOpenArrays()
+
+
 def test_write_output_buckets(da, tmp_path):
     """One output partition per bucket, sized by the boundaries (element indices -> bytes; data.py:289-298)."""
     da.SetDistribMount(tmp_path)
