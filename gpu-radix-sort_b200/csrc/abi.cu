@@ -16,6 +16,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <thread>
 #include <vector>
 
 #include <cuda_profiler_api.h>
@@ -626,17 +627,31 @@ API int libsortDistribSort(uint32_t *h_keys, size_t n, int ngpu)
     // 1. shards to the GPUs, a stratified sample of each
     static std::atomic<uint32_t> seed{1};
     const uint32_t sd = seed.fetch_add(1);
-    for (int g = 0; g < P; g++) {
-        DeviceCtx &c = *cs[g];
-        if (!cuda_ok(cudaSetDevice(c.dev), "cudaSetDevice")) return 0;
-        if (!ensure_capacity(c, shard + shard / 4, 0) || !dist_small_buffers(c, P, g == 0)) return 0;
-        if (!c.copier.to_device(c.a, h_keys + (size_t)g * shard, shard_len(g) * sizeof(uint32_t), c.stream)) return 0;
-        if (!cuda_ok(sample_keys(c.a, shard_len(g), c.small, kDistSamples, sd, c.stream), "sample")) return 0;
-        if (!cuda_ok(cudaMemcpyPeerAsync(cs[0]->gather + (size_t)g * kDistSamples, cs[0]->dev, c.small, c.dev,
-                                         kDistSamples * sizeof(uint32_t), c.stream),
-                     "cudaMemcpyPeerAsync(samples)"))
-            return 0;
+    // (one host thread per GPU: a pageable caller buffer is staged chunk by chunk and to_device blocks
+    // until its GPU has everything, so a single thread would feed the GPUs one after the other)
+    for (int g = 0; g < P; g++) {  // buffers first, GPU 0's gather buffer is everybody's target
+        if (!cuda_ok(cudaSetDevice(cs[g]->dev), "cudaSetDevice")) return 0;
+        if (!ensure_capacity(*cs[g], shard + shard / 4, 0) || !dist_small_buffers(*cs[g], P, g == 0)) return 0;
     }
+    auto per_gpu = [&](auto &&fn) {
+        std::atomic<int> ok{1};
+        std::vector<std::thread> th;
+        for (int g = 0; g < P; g++)
+            th.emplace_back([&, g] {
+                if (!cuda_ok(cudaSetDevice(cs[g]->dev), "cudaSetDevice") || !fn(g)) ok.store(0);
+            });
+        for (auto &t : th) t.join();
+        return ok.load() != 0;
+    };
+    if (!per_gpu([&](int g) {
+            DeviceCtx &c = *cs[g];
+            if (!c.copier.to_device(c.a, h_keys + (size_t)g * shard, shard_len(g) * sizeof(uint32_t), c.stream)) return false;
+            if (!cuda_ok(sample_keys(c.a, shard_len(g), c.small, kDistSamples, sd, c.stream), "sample")) return false;
+            return cuda_ok(cudaMemcpyPeerAsync(cs[0]->gather + (size_t)g * kDistSamples, cs[0]->dev, c.small, c.dev,
+                                               kDistSamples * sizeof(uint32_t), c.stream),
+                           "cudaMemcpyPeerAsync(samples)");
+        }))
+        return 0;
     if (!dist_sync_all(cs, P, "sync(samples)")) return 0;
 
     // 2. splitters = quantiles of the sorted sample (GPU 0), handed to every GPU
@@ -718,18 +733,20 @@ API int libsortDistribSort(uint32_t *h_keys, size_t n, int ngpu)
         if (!ensure_capacity(*cs[d], totals[d], 0)) return 0;  // the shard in c.a is no longer needed
         if (!local_sort(d)) return 0;
     }
-    size_t first = 0;
+    size_t first = 0, firsts[kDistMaxGpus];
     for (int d = 0; d < P; d++) {
-        DeviceCtx &c = *cs[d];
-        if (totals[d]) {
-            if (!cuda_ok(cudaSetDevice(c.dev), "cudaSetDevice")) return 0;
-            bool violated = false;
-            if (!cuda_ok(rank_audit(c.stream, &violated), "rank audit")) return 0;
-            if (violated && !local_sort(d)) return 0;
-            if (!c.copier.to_host(h_keys + first, sorted[d], totals[d] * sizeof(uint32_t), c.stream)) return 0;
-        }
+        firsts[d] = first;
         first += totals[d];
     }
+    if (!per_gpu([&](int d) {
+            DeviceCtx &c = *cs[d];
+            if (!totals[d]) return true;
+            bool violated = false;
+            if (!cuda_ok(rank_audit(c.stream, &violated), "rank audit")) return false;
+            if (violated && !local_sort(d)) return false;
+            return c.copier.to_host(h_keys + firsts[d], sorted[d], totals[d] * sizeof(uint32_t), c.stream);
+        }))
+        return 0;
     if (first != n) {
         fprintf(stderr, "libsort: distributed sort lost keys (%zu of %zu arrived)\n", first, n);
         return 0;
