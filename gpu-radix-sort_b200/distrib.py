@@ -266,9 +266,9 @@ class DistributedSorter:
         binding.check(L.libsortDeviceSortDyn(self.recv_ptr, self.out.data_ptr(), self.tmp.data_ptr(), self.cap,
                                              self.d_nrecv.data_ptr(), self.ws.data_ptr(), self.ws.numel(), st,
                                              ctypes.byref(times) if times is not None else None), "local sort")
-        if W > 1:
-            # the receive buffer is overwritten by the next sort's remote stores: fence it
-            dist.all_reduce(self.token, group=self.group)
+        # No fence here: the receive buffer is next written by the NEXT sort's exchange, and every exchange
+        # comes after that sort's all-gather (histograms or samples), which no rank can leave before every
+        # rank -- stream-ordered behind its local sort above -- has entered it.
         if ev:
             ev("local_sort")
         return self.out, self.d_nrecv
@@ -309,9 +309,8 @@ class DistributedSorter:
                                              self.cursor.data_ptr(), self.ws.data_ptr(), self.ws.numel(), st,
                                              ctypes.byref(times) if times is not None else None), "local sort")
         self.d_nrecv.copy_(self.cursor[:1])
-        self.cursor[:1].zero_()                             # ready for the next exchange ...
-        if W > 1:
-            dist.all_reduce(self.token, group=self.group)   # ... which nobody starts before this fence
+        self.cursor[:1].zero_()                             # ready for the next exchange, which nobody starts before
+        #                                                     the next sort's sample all-gather (see sort_async)
         if ev:
             ev("local_sort")
         return self.out, self.d_nrecv
