@@ -264,8 +264,11 @@ def test_cxx_consumers(gpu_lib, pkg):
         assert r.returncode == 0 and "Partial sort (16b)" in r.stdout, r.stdout + r.stderr
 
 
-@pytest.mark.parametrize("env", [{}, {"LIBSORT_RANK": "ballot"}, {"LIBSORT_BULK_OUT": "1"}, {"LIBSORT_RANK": "atoms"}],
-                         ids=["default", "ballot", "bulk_out", "atoms_forced"])
+@pytest.mark.parametrize("env", [{}, {"LIBSORT_RANK": "ballot"}, {"LIBSORT_BULK_OUT": "1"}, {"LIBSORT_RANK": "atoms"},
+                                 {"LIBSORT_PDL": "0"}, {"LIBSORT_SMALL_PATH": "0"}, {"LIBSORT_K3": "inp256x56p"},
+                                 {"LIBSORT_K3": "pipe42w"}],
+                         ids=["default", "ballot", "bulk_out", "atoms_forced", "no_dependent_launch", "no_small_tiles",
+                              "k3_bulk_inplace", "k3_pipeline"])
 def test_kernel_variants(env):
     """Every compiled scatter kernel (ranking mode x write-out) against the oracle, multi-tile
     skewed inputs included; the variant is fixed when the library is first used, hence a fresh process."""
