@@ -91,6 +91,8 @@ constexpr int kTileSplitBulk = SORT_THREADS * SPLIT_KPT;
 // the radix scatter writing into an array sliced over several GPUs (step-wise distributed LSD sort)
 #define KERNEL_SLICED_A k_onesweep<SORT_THREADS, SORT_KPT, SORT_MINB, RANK_ATOMS, 0, SORT_LB, RadixBinner, OUT_SLICED>
 #define KERNEL_SLICED_B k_onesweep<SORT_THREADS, BALLOT_KPT, SPLIT_MINB, RANK_BALLOT, 0, SORT_LB, RadixBinner, OUT_SLICED>
+#define KERNEL_SLICED_BULK \
+    k_onesweep_bulk<SORT_THREADS, SORT_KPT, SORT_MINB, SORT_LB, RANK_ATOMS, RadixBinner, false, EXCH_ORDERED, true>
 using SmemSlicedA = OnesweepSmem<SORT_THREADS, SORT_KPT, OUT_SLICED, RadixBinner::Arg>;
 using SmemSlicedB = OnesweepSmem<SORT_THREADS, BALLOT_KPT, OUT_SLICED, RadixBinner::Arg>;
 
@@ -177,7 +179,7 @@ struct DevInfo {
     int sms = 0;
     int occ_s = 0;  // the small-input scatter kernel
     int occ_a = 0, occ_b = 0, occ_split = 0, occ_bulk = 0, occ_split_bulk = 0;  // resident CTAs per SM of the three scatter kernels
-    int occ_sliced_a = 0, occ_sliced_b = 0;
+    int occ_sliced_a = 0, occ_sliced_b = 0, occ_sliced_bulk = 0;
     int occ_k3[32] = {};
     int hist_occ = 0;
     bool rank_atoms = false;  // rank keys with returning shared atomics (self-tested) instead of ballots
@@ -195,6 +197,7 @@ static const int g_hist_mode = env_int("LIBSORT_HIST_MODE", 1);
 // 1 = bulk-copy write-out of the scatter pass (k_onesweep_bulk), 0 = LDS + STG write-out (k_onesweep)
 static const int g_bulk_out = env_int("LIBSORT_BULK_OUT", 0);
 static const int g_pdl = env_int("LIBSORT_PDL", 1);  // programmatic dependent launch between the kernels of one sort
+static const int g_bulk_step = env_int("LIBSORT_BULK_STEP", 0);  // 1: step-wise distributed sort writes its runs through the bulk-copy engine (slower: 8.09 vs 6.55 ms at 2 GPUs)
 static const int g_small_path = env_int("LIBSORT_SMALL_PATH", 1);  // 0: big tiles at every size (A/B measurements)
 // the same choice for the splitter scatter of the distributed sort (runs of kilobytes, peer destinations)
 static const int g_bulk_exchange = env_int("LIBSORT_BULK_EXCHANGE", 1);
@@ -301,6 +304,7 @@ static cudaError_t dev_info(DevInfo **out)
             {(const void *)KERNEL_B(8), (int)sizeof(SmemB)},     {(const void *)KERNEL_B(0), (int)sizeof(SmemB)},
             {(const void *)KERNEL_SPLIT(1), (int)sizeof(SmemSplit)},  {(const void *)KERNEL_SPLIT(3), (int)sizeof(SmemSplit)},
             {(const void *)KERNEL_SPLIT(7), (int)sizeof(SmemSplit)},  {(const void *)KERNEL_SPLIT(15), (int)sizeof(SmemSplit)},
+            {(const void *)KERNEL_SLICED_BULK, (int)sizeof(SmemBulk)},
             {(const void *)KERNEL_SLICED_A, (int)sizeof(SmemSlicedA)}, {(const void *)KERNEL_SLICED_B, (int)sizeof(SmemSlicedB)}};
         for (auto &k : kernels) {
             e = cudaFuncSetAttribute(k.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, k.smem);
@@ -326,6 +330,8 @@ static cudaError_t dev_info(DevInfo **out)
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.occ_b, KERNEL_B(8), SORT_THREADS, sizeof(SmemB));
         if (e != cudaSuccess) return e;
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.occ_split, KERNEL_SPLIT(15), SORT_THREADS, sizeof(SmemSplit));
+        if (e != cudaSuccess) return e;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.occ_sliced_bulk, KERNEL_SLICED_BULK, SORT_THREADS, sizeof(SmemBulk));
         if (e != cudaSuccess) return e;
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.occ_sliced_a, KERNEL_SLICED_A, SORT_THREADS, sizeof(SmemSlicedA));
         if (e != cudaSuccess) return e;
@@ -826,7 +832,11 @@ cudaError_t step_scatter(const uint32_t *in, size_t n, uint32_t shift, uint32_t 
     CK(cudaMemsetAsync(ws + WS_TICKET, 0, (WS_DESC - WS_TICKET + ntiles * RADIX) * sizeof(uint32_t), st));
     const RadixBinner::Arg arg{shift, (1u << nbits) - 1};
     const int use_tma = (reinterpret_cast<uintptr_t>(in) & 15u) == 0;
-    if (dev->rank_atoms) {
+    if (dev->rank_atoms && g_bulk_step && dev->occ_sliced_bulk > 0) {
+        const int grid = (int)std::min<size_t>(ntiles, (size_t)dev->sms * dev->occ_sliced_bulk);
+        KERNEL_SLICED_BULK<<<grid, SORT_THREADS, sizeof(SmemBulk), st>>>(in, nullptr, (uint32_t)n, arg, d_table, nullptr, ws + WS_DESC,
+                                                                        ws + WS_TICKET, (uint32_t)ntiles, use_tma);
+    } else if (dev->rank_atoms) {
         const int grid = (int)std::min<size_t>(ntiles, (size_t)dev->sms * dev->occ_sliced_a);
         KERNEL_SLICED_A<<<grid, SORT_THREADS, sizeof(SmemSlicedA), st>>>(in, nullptr, (uint32_t)n, arg, d_table, nullptr,
                                                                          ws + WS_DESC, ws + WS_TICKET, (uint32_t)ntiles, use_tma, nullptr);

@@ -81,7 +81,14 @@ __global__ void k_store_cursor_plan(const unsigned long long *__restrict__ peer_
     }
 }
 
-template <int THREADS, int KPT, int MINB, int LB, int RANK, class Binner, bool PTR_OUT, int UNORDERED = EXCH_ORDERED>
+// SLICED (step-wise distributed sort): base_v is a SliceTable -- bucket bases are positions in ONE array cut
+// into slices that live on different GPUs (k_onesweep<OUT_SLICED> is the per-key-store version).  A
+// bucket's run in a tile starts at a global position inside slice j; the part that fits goes to slice
+// j's owner through the bulk-copy engine like any run, the rare rest (a run crosses at most one slice
+// boundary, and only the one tile whose run covers the boundary does) is stored key by key at the start
+// of slice j + 1.
+template <int THREADS, int KPT, int MINB, int LB, int RANK, class Binner, bool PTR_OUT, int UNORDERED = EXCH_ORDERED,
+          bool SLICED = false>
 __global__ void __launch_bounds__(THREADS, MINB)
     k_onesweep_bulk(const uint32_t *__restrict__ in, uint32_t *__restrict__ out, uint32_t n, const typename Binner::Arg binner_arg,
                     const void *__restrict__ base_v, uint32_t *__restrict__ base_next, uint32_t *__restrict__ desc,
@@ -95,7 +102,8 @@ __global__ void __launch_bounds__(THREADS, MINB)
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Smem &s = *reinterpret_cast<Smem *>(smem_raw);
 
-    if (!PTR_OUT && ticket[SKIP_OFFSET]) {  // constant digit (k_scan_hist): the pass is a copy
+    static_assert(!SLICED || (!PTR_OUT && UNORDERED == EXCH_ORDERED), "sliced output: ordered radix pass");
+    if (!PTR_OUT && !SLICED && ticket[SKIP_OFFSET]) {  // constant digit (k_scan_hist): the pass is a copy
         copy_keys(in, out, n);
         return;
     }
@@ -173,6 +181,8 @@ __global__ void __launch_bounds__(THREADS, MINB)
         //     look-back, then lay the buckets out with the 16-byte phase of their destinations
         uint32_t my_count = 0, padded = 0, phase = 0, span4 = 0;
         bool drop = false;  // EXCH_REMOTE_CURSOR: the destination is full, this run is not stored
+        uint32_t lo_len = 0;               // SLICED: keys of this run that belong to the slice it starts in
+        unsigned long long hi_addr = 0;    // SLICED: first key of the next slice (where the rest goes)
         unsigned long long dst_addr = 0;  // byte address of the first destination of this tile's run
         if (tid < RADIX) {
 #pragma unroll
@@ -218,6 +228,14 @@ __global__ void __launch_bounds__(THREADS, MINB)
             }
             if (PTR_OUT && UNORDERED == EXCH_REMOTE_CURSOR) {
                 dst_addr = my_count ? static_cast<const CursorPlan *>(base_v)->dest[tid] + 4ull * excl : 0ull;
+            } else if (SLICED) {
+                const SliceTable *tab = static_cast<const SliceTable *>(base_v);
+                const uint32_t g = tab->gbase[tid] + excl, ns = tab->nslice;
+                uint32_t j = 0;
+                for (uint32_t k = 1; k < ns; k++) j += g >= tab->slice_start[k] ? 1u : 0u;
+                dst_addr = tab->peer[j] + 4ull * (unsigned long long)(g - tab->slice_start[j]);
+                lo_len = min(my_count, tab->slice_start[j + 1] - g);
+                hi_addr = j + 1 < ns ? tab->peer[j + 1] : 0ull;
             } else if (PTR_OUT) {
                 dst_addr = static_cast<const unsigned long long *>(base_v)[tid] + 4ull * excl;
             } else {
@@ -287,10 +305,13 @@ __global__ void __launch_bounds__(THREADS, MINB)
         if (tid < RADIX && my_count && !drop) {
             const uint32_t *src = reinterpret_cast<const uint32_t *>(tile_bytes + start4);
             uint32_t *dst = reinterpret_cast<uint32_t *>(dst_addr);
-            const uint32_t head = min(my_count, (4u - phase) & 3u);
-            const uint32_t body = (my_count - head) & ~3u;
+            const uint32_t here = SLICED ? lo_len : my_count;  // keys for the destination the run starts in
+            const uint32_t head = min(here, (4u - phase) & 3u);
+            const uint32_t body = (here - head) & ~3u;
             for (uint32_t j = 0; j < head; j++) dst[j] = src[j];
-            for (uint32_t j = head + body; j < my_count; j++) dst[j] = src[j];
+            for (uint32_t j = head + body; j < here; j++) dst[j] = src[j];
+            if (SLICED)  // the run crosses into the next slice (one tile per slice boundary and bucket)
+                for (uint32_t j = here; j < my_count; j++) reinterpret_cast<uint32_t *>(hi_addr)[j - here] = src[j];
             if (body) {
                 fence_proxy_async();  // the generic-proxy stores of (4) come before the engine's reads
                 bulk_store(dst + head, src + head, body * 4u);
