@@ -66,7 +66,7 @@ namespace b200sort {
 #define SMALL_MINB 4
 #endif
 constexpr int kTileS = SORT_THREADS * SMALL_KPT;
-constexpr size_t kSmallNMax = (size_t)1 << 21;
+constexpr size_t kSmallNMax = (size_t)1 << 23;  // workspace is sized for short tiles up to here; LIBSORT_SMALL_MAX picks the actual limit
 constexpr int kTileA = SORT_THREADS * SORT_KPT;
 constexpr int kTileB = SORT_THREADS * BALLOT_KPT;
 constexpr int kTileMin = kTileA < kTileB ? kTileA : kTileB;
@@ -198,6 +198,7 @@ static const int g_hist_mode = env_int("LIBSORT_HIST_MODE", 1);
 static const int g_bulk_out = env_int("LIBSORT_BULK_OUT", 0);
 static const int g_pdl = env_int("LIBSORT_PDL", 1);  // programmatic dependent launch between the kernels of one sort
 static const int g_bulk_step = env_int("LIBSORT_BULK_STEP", 0);  // 1: step-wise distributed sort writes its runs through the bulk-copy engine (slower: 8.09 vs 6.55 ms at 2 GPUs)
+static const int g_small_max = env_int("LIBSORT_SMALL_MAX", 1 << 22);  // inputs up to this many keys use the 4096-key tiles (break-even ~4 M keys)
 static const int g_small_path = env_int("LIBSORT_SMALL_PATH", 1);  // 0: big tiles at every size (A/B measurements)
 // the same choice for the splitter scatter of the distributed sort (runs of kilobytes, peer destinations)
 static const int g_bulk_exchange = env_int("LIBSORT_BULK_EXCHANGE", 1);
@@ -476,7 +477,7 @@ cudaError_t sort_bits(const uint32_t *in, uint32_t *a, uint32_t *b, uint32_t *wa
     const int k3 = (!dyn_n && dev->rank_atoms && k3_selected() >= 0 && dev->occ_k3[k3_selected()] > 0) ? k3_selected() : -1;
     // small input: more, shorter tiles (not with the debug portion override, whose tests count big tiles)
     const bool small = g_small_path && !dyn_n && k3 < 0 && dev->rank_atoms && dev->occ_s > 0 && n <= kSmallNMax &&
-                       n < (size_t)dev->sms * kTileA && g_portion_tiles.load() == 0;
+                       n <= (size_t)g_small_max && g_portion_tiles.load() == 0;
     const int tile = small ? kTileS : k3 >= 0 ? g_k3[k3].tile : dev->rank_atoms ? kTileA : kTileB;
     const size_t ntiles = num_tiles(n, tile);
     const uint32_t ptiles = portion_tiles(tile);
