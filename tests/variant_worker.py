@@ -27,7 +27,7 @@ def cases(n):
 
 
 bad = 0
-for n in (1, 4099, 14336, 14337, 200003, (1 << 20) + 5, (1 << 21) + 4099):   # the last one is past the small-input path
+for n in (1, 4099, 14336, 14337, 200003, (1 << 20) + 5, (1 << 22) + 4099):   # the last one is past the small-input path (2^22 keys)
     for name, k in cases(n):
         got = k.copy()
         assert lib.providedGpu(got.ctypes.data, n)
