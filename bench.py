@@ -543,7 +543,7 @@ def run_multi(args, rank, world, local_rank):
     distrib = importlib.import_module("gpu-radix-sort_b200.distrib")
     torch.cuda.set_device(local_rank)
     import datetime
-    dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank), timeout=datetime.timedelta(seconds=90))
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank), timeout=datetime.timedelta(seconds=180))
     n = args.keys
     # one continuous PCG stream; rank g owns elements [g*n, (g+1)*n)  
     clocks = ClockSampler(local_rank)
