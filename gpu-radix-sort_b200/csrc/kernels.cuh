@@ -452,6 +452,105 @@ static __device__ unsigned int g_rank_violation = 0;
 constexpr int RANK_BALLOT = 0;  // one vote.ballot per digit bit + a leader atomic: architecturally ordered
 constexpr int RANK_ATOMS = 1;   // rank = return value of the warp's shared atomic (see DESIGN.md "atomic ranking")
 
+// ---- phases shared by k_onesweep and k_onesweep_bulk (onesweep_bulk.cuh) ----------------------
+// (1) the tile's keys -> registers, warp-striped so that tile order == rank order.  With use_tma the
+// 16-byte-multiple part of the tile has landed in s.keys (mbarrier phase `parity`); a ragged tail
+// (<= 3 keys, last tile only) is read straight from global; positions past `valid` become 0xFFFFFFFF.
+template <int KPT, int TILE, class Smem>
+__device__ __forceinline__ void tile_keys_to_registers(uint32_t (&key)[KPT], Smem &s, const uint32_t *__restrict__ in,
+                                                       uint32_t tile_base, uint32_t valid, uint32_t wbase, int use_tma,
+                                                       uint32_t parity)
+{
+    if (use_tma) {
+        mbar_wait(&s.mbar, parity);
+        if (valid == TILE) {
+#pragma unroll
+            for (int i = 0; i < KPT; i++) key[i] = s.keys[wbase + i * 32];
+        } else {
+            const uint32_t staged = ((valid * 4u) & ~15u) >> 2;
+#pragma unroll
+            for (int i = 0; i < KPT; i++) {
+                const uint32_t idx = wbase + i * 32;
+                key[i] = idx < staged ? s.keys[idx] : (idx < valid ? in[(size_t)tile_base + idx] : 0xffffffffu);
+            }
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < KPT; i++) {
+            const uint32_t idx = wbase + i * 32;
+            key[i] = idx < valid ? in[(size_t)tile_base + idx] : 0xffffffffu;
+        }
+    }
+    __syncwarp();  // this warp's counters were zeroed by other lanes
+}
+
+// (2) early counts: per-warp digit histogram (adding 1 lets same-digit lanes be merged).  Indexed with
+// bin(), not bin4(): a different expression than (4) uses, so that the optimiser recomputes the address
+// there instead of spilling KPT of them across barriers.  A splitter bin costs a binary search and
+// depends on the position: it is kept, 4 bits per key, in dig[].
+template <class Binner, int KPT, int NDIG>
+__device__ __forceinline__ void tile_count_digits(const uint32_t (&key)[KPT], uint32_t (&dig)[NDIG], const Binner &binner,
+                                                  uint32_t *warp_hist, uint32_t first_pos)
+{
+#pragma unroll
+    for (int i = 0; i < KPT; i++) {
+        const uint32_t d = binner.bin(key[i], first_pos + i * 32);
+        atomicAdd(&warp_hist[d], 1u);
+        if (Binner::kByPosition) dig[i >> 3] |= d << (4 * (i & 7));
+    }
+}
+
+// (4) rank every key of the tile and move it to its place in the digit-sorted tile.  warp counters hold
+// running BYTE offsets into the tile buffer.  RANK_ATOMS: a key's place is the value its warp's shared
+// atomicAdd returns (see DESIGN.md "atomic ranking"); one row of every tile is re-checked with ballots
+// (the audit: lanes of one instruction with the same digit must have been served in ascending lane
+// order; a violation raises g_rank_violation and the host side repeats the call with the ballot
+// kernels, engine.cu rank_audit).  A tile in which one digit dominates (`heavy`) takes the out-of-line
+// path.  RANK_BALLOT: one vote per digit bit + a leader atomic.  first_pos = position of key[0].
+template <int RANK, int NBITS, class Binner, int KPT, class Smem, int NDIG>
+__device__ __forceinline__ void tile_rank_and_place(const uint32_t (&key)[KPT], const uint32_t (&dig)[NDIG], const Binner &binner,
+                                                    Smem &s, unsigned char *my_hist, unsigned char *tile_bytes, int heavy,
+                                                    uint32_t first_pos)
+{
+    if (RANK == RANK_ATOMS) {
+        if (!heavy) {
+#pragma unroll
+            for (int i = 0; i < KPT; i++) {
+                const uint32_t p4 = atomicAdd(reinterpret_cast<uint32_t *>(my_hist + binner.bin4(key[i], first_pos + i * 32)), 4u);
+                *reinterpret_cast<uint32_t *>(tile_bytes + p4) = key[i];
+                if (i == 0) {  // the audit row (1/KPT of the keys)
+                    const uint32_t d4 = binner.bin4(key[0], first_pos);
+                    const uint32_t peers = match_digit<NBITS>(d4 >> 2, binner.nbits());
+                    const uint32_t first = __shfl_sync(0xffffffffu, p4, __ffs(peers) - 1);
+                    if (p4 != first + 4u * __popc(peers & lanemask_lt())) atomicOr(&g_rank_violation, 1u);
+                }
+            }
+        } else {
+            // one digit dominates the tile (skewed input): out-of-line path, see rank_tile_heavy
+            uint32_t spilled[KPT];
+#pragma unroll
+            for (int i = 0; i < KPT; i++) spilled[i] = key[i];
+            rank_tile_heavy<Binner, Smem>(spilled, &s);
+        }
+    } else {
+        const uint32_t lt = lanemask_lt();
+        const int lane = threadIdx.x & 31;
+        const int nbits = binner.nbits();
+        const uint32_t hist_addr = smem_u32(my_hist);
+#pragma unroll
+        for (int i = 0; i < KPT; i++) {
+            const uint32_t d4 = Binner::kByPosition ? ((dig[i >> 3] >> (4 * (i & 7))) & 15u) << 2
+                                                    : binner.bin4(key[i], first_pos + i * 32);
+            const uint32_t peers = match_digit<(Binner::kBits ? Binner::kBits : NBITS)>(d4 >> 2, nbits);
+            const uint32_t before = __popc(peers & lt);
+            const int top = 31 - __clz(peers);  // highest peer lane leads; its `before` + 1 is the group size
+            uint32_t off4 = leader_atom_add(hist_addr + d4, (before + 1u) * 4u, lane == top);
+            off4 = __shfl_sync(0xffffffffu, off4, top);
+            *reinterpret_cast<uint32_t *>(tile_bytes + off4 + before * 4u) = key[i];
+        }
+    }
+}
+
 // in/out: this portion's keys (n < 2^30 so that counts fit the 30-bit
 // descriptor value).  base: global bucket bases for this portion;
 // base_next (nullable): receives base + portion bucket totals for the next
@@ -536,42 +635,12 @@ __global__ void __launch_bounds__(THREADS, MINB)
         const uint32_t tile_base = cur * (uint32_t)TILE;
         const uint32_t valid = min((uint32_t)TILE, n - tile_base);
 
-        // (1) keys -> registers, warp-striped so that tile order == rank order
+        // (1) keys -> registers, (2) early per-warp digit counts (helpers above)
         uint32_t key[KPT];
         const uint32_t wbase = warp * (KPT * 32) + lane;
-        if (use_tma) {
-            mbar_wait(&s.mbar, it & 1);
-            if (valid == TILE) {
-#pragma unroll
-                for (int i = 0; i < KPT; i++) key[i] = s.keys[wbase + i * 32];
-            } else {
-                const uint32_t staged = ((valid * 4u) & ~15u) >> 2;
-#pragma unroll
-                for (int i = 0; i < KPT; i++) {
-                    const uint32_t idx = wbase + i * 32;
-                    key[i] = idx < staged ? s.keys[idx] : (idx < valid ? in[(size_t)tile_base + idx] : 0xffffffffu);
-                }
-            }
-        } else {
-#pragma unroll
-            for (int i = 0; i < KPT; i++) {
-                const uint32_t idx = wbase + i * 32;
-                key[i] = idx < valid ? in[(size_t)tile_base + idx] : 0xffffffffu;
-            }
-        }
-        __syncwarp();  // this warp's counters were zeroed by other lanes
-
-        // (2) early counts: per-warp digit histogram (adding 1 lets same-digit lanes be merged)
-        //     (indexed with bin(), not bin4(): a different expression than (4) uses, so that the
-        //     optimiser recomputes the address there instead of spilling KPT of them across barriers).
-        //     A splitter bin costs a binary search and depends on the position: kept, 4 bits per key.
+        tile_keys_to_registers<KPT, TILE>(key, s, in, tile_base, valid, wbase, use_tma, it & 1);
         uint32_t dig[Binner::kByPosition ? (KPT + 7) / 8 : 1] = {};
-#pragma unroll
-        for (int i = 0; i < KPT; i++) {
-            const uint32_t d = binner.bin(key[i], tile_base + wbase + i * 32);
-            atomicAdd(&s.warp_hist[warp][d], 1u);
-            if (Binner::kByPosition) dig[i >> 3] |= d << (4 * (i & 7));
-        }
+        tile_count_digits(key, dig, binner, s.warp_hist[warp], tile_base + wbase);
         __syncthreads();
 
         // (3) bin threads: reduce over warps, publish the tile aggregate,
@@ -607,50 +676,9 @@ __global__ void __launch_bounds__(THREADS, MINB)
         if (is_heavy) s.heavy_d4 = (uint32_t)tid * 4u;  // up to three candidates: any one will do
         const int heavy = __syncthreads_or(is_heavy);
 
-        // (4) rank every key and move it to its place in the digit-sorted tile
-        //     (all warps hold their keys in registers since (2), so the landing
-        //     buffer can be overwritten)
-        if (RANK == RANK_ATOMS) {
-            if (!heavy) {
-#pragma unroll
-                for (int i = 0; i < KPT; i++) {
-                    const uint32_t p4 =
-                        atomicAdd(reinterpret_cast<uint32_t *>(my_hist + binner.bin4(key[i], tile_base + wbase + i * 32)), 4u);
-                    *reinterpret_cast<uint32_t *>(tile_bytes + p4) = key[i];
-                    if (i == 0) {
-                        // audit of the lane-order assumption on one row of every tile (1/KPT of the
-                        // keys): lanes of this instruction with the same digit must have been served
-                        // in ascending lane order.  A violation raises g_rank_violation; the host side
-                        // then repeats the call with the ballot kernels (engine.cu rank_audit).
-                        const uint32_t d4 = binner.bin4(key[0], tile_base + wbase);
-                        const uint32_t peers = match_digit<NBITS>(d4 >> 2, binner.nbits());
-                        const uint32_t first = __shfl_sync(0xffffffffu, p4, __ffs(peers) - 1);
-                        if (p4 != first + 4u * __popc(peers & lanemask_lt())) atomicOr(&g_rank_violation, 1u);
-                    }
-                }
-            } else {
-                // one digit dominates the tile (skewed input): out-of-line path, see rank_tile_heavy
-                uint32_t spilled[KPT];
-#pragma unroll
-                for (int i = 0; i < KPT; i++) spilled[i] = key[i];
-                rank_tile_heavy<Binner, Smem>(spilled, &s);
-            }
-        } else {
-            const uint32_t lt = lanemask_lt();
-            const int nbits = binner.nbits();
-            const uint32_t hist_addr = smem_u32(my_hist);
-#pragma unroll
-            for (int i = 0; i < KPT; i++) {
-                const uint32_t d4 = Binner::kByPosition ? ((dig[i >> 3] >> (4 * (i & 7))) & 15u) << 2
-                                                        : binner.bin4(key[i], tile_base + wbase + i * 32);
-                const uint32_t peers = match_digit<(Binner::kBits ? Binner::kBits : NBITS)>(d4 >> 2, nbits);
-                const uint32_t before = __popc(peers & lt);
-                const int top = 31 - __clz(peers);  // highest peer lane leads; its `before` + 1 is the group size
-                uint32_t off4 = leader_atom_add(hist_addr + d4, (before + 1u) * 4u, lane == top);
-                off4 = __shfl_sync(0xffffffffu, off4, top);
-                *reinterpret_cast<uint32_t *>(tile_bytes + off4 + before * 4u) = key[i];
-            }
-        }
+        // (4) rank every key and move it to its place in the digit-sorted tile (all warps hold their
+        //     keys in registers since (2), so the landing buffer can be overwritten)
+        tile_rank_and_place<RANK, NBITS, Binner, KPT, Smem>(key, dig, binner, s, my_hist, tile_bytes, heavy, tile_base + wbase);
 
         // (5) decoupled look-back for this thread's bin
         if (tid < RADIX) {

@@ -141,40 +141,12 @@ __global__ void __launch_bounds__(THREADS, MINB)
         const uint32_t tile_base = cur * (uint32_t)TILE;
         const uint32_t valid = min((uint32_t)TILE, n - tile_base);
 
-        // (1) keys -> registers, warp-striped so that tile order == rank order
+        // (1) keys -> registers, (2) early per-warp digit counts (shared with k_onesweep, kernels.cuh)
         uint32_t key[KPT];
         const uint32_t wbase = warp * (KPT * 32) + lane;
-        if (use_tma) {
-            mbar_wait(&s.mbar, it & 1);
-            if (valid == TILE) {
-#pragma unroll
-                for (int i = 0; i < KPT; i++) key[i] = s.keys[wbase + i * 32];
-            } else {
-                const uint32_t staged = ((valid * 4u) & ~15u) >> 2;
-#pragma unroll
-                for (int i = 0; i < KPT; i++) {
-                    const uint32_t idx = wbase + i * 32;
-                    key[i] = idx < staged ? s.keys[idx] : (idx < valid ? in[(size_t)tile_base + idx] : 0xffffffffu);
-                }
-            }
-        } else {
-#pragma unroll
-            for (int i = 0; i < KPT; i++) {
-                const uint32_t idx = wbase + i * 32;
-                key[i] = idx < valid ? in[(size_t)tile_base + idx] : 0xffffffffu;
-            }
-        }
-        __syncwarp();  // this warp's counters were zeroed by other lanes
-
-        // (2) early counts: per-warp digit histogram (see k_onesweep for the bin()/bin4() note).
-        //     A splitter bin costs a binary search (and depends on the position): keep it, 4 bits per key.
+        tile_keys_to_registers<KPT, TILE>(key, s, in, tile_base, valid, wbase, use_tma, it & 1);
         uint32_t dig[Binner::kByPosition ? (KPT + 7) / 8 : 1] = {};
-#pragma unroll
-        for (int i = 0; i < KPT; i++) {
-            const uint32_t d = binner.bin(key[i], tile_base + wbase + i * 32);
-            atomicAdd(&s.warp_hist[warp][d], 1u);
-            if (Binner::kByPosition) dig[i >> 3] |= d << (4 * (i & 7));
-        }
+        tile_count_digits(key, dig, binner, s.warp_hist[warp], tile_base + wbase);
         __syncthreads();
 
         // (3) bin threads: reduce over warps, publish the tile aggregate, finish the
@@ -261,37 +233,8 @@ __global__ void __launch_bounds__(THREADS, MINB)
         }
         const int heavy = __syncthreads_or(is_heavy);
 
-        // (4) rank every key and move it to its place in the padded digit-sorted tile
-        if (RANK == RANK_ATOMS) {
-            if (!heavy) {
-#pragma unroll
-                for (int i = 0; i < KPT; i++) {
-                    const uint32_t p4 =
-                        atomicAdd(reinterpret_cast<uint32_t *>(my_hist + binner.bin4(key[i], tile_base + wbase + i * 32)), 4u);
-                    *reinterpret_cast<uint32_t *>(tile_bytes + p4) = key[i];
-                }
-            } else {
-                uint32_t spilled[KPT];
-#pragma unroll
-                for (int i = 0; i < KPT; i++) spilled[i] = key[i];
-                rank_tile_heavy<Binner, Smem>(spilled, &s);
-            }
-        } else {
-            const uint32_t lt = lanemask_lt();
-            const int nbits = binner.nbits();
-            const uint32_t hist_addr = smem_u32(my_hist);
-#pragma unroll
-            for (int i = 0; i < KPT; i++) {
-                const uint32_t d4 = Binner::kByPosition ? ((dig[i >> 3] >> (4 * (i & 7))) & 15u) << 2
-                                                        : binner.bin4(key[i], tile_base + wbase + i * 32);
-                const uint32_t peers = match_digit<Binner::kBits>(d4 >> 2, nbits);
-                const uint32_t before = __popc(peers & lt);
-                const int top = 31 - __clz(peers);  // highest peer lane leads; its `before` + 1 is the group size
-                uint32_t off4 = leader_atom_add(hist_addr + d4, (before + 1u) * 4u, lane == top);
-                off4 = __shfl_sync(0xffffffffu, off4, top);
-                *reinterpret_cast<uint32_t *>(tile_bytes + off4 + before * 4u) = key[i];
-            }
-        }
+        // (4) rank every key and move it to its place in the padded digit-sorted tile (shared with k_onesweep)
+        tile_rank_and_place<RANK, 0, Binner, KPT, Smem>(key, dig, binner, s, my_hist, tile_bytes, heavy, tile_base + wbase);
         __syncwarp();
 #pragma unroll
         for (int j = lane; j < RADIX; j += 32) s.warp_hist[warp][j] = 0;
