@@ -16,7 +16,7 @@ ADDITIVE_SYMBOLS = ["libsortTileKeys", "libsortWorkspaceBytes", "libsortDeviceSo
                     "libsortStepTableBytes", "libsortStepTableInit", "libsortStepCounts", "libsortStepBases", "libsortStepScatter",
                     "libsortRankAudit", "libsortDeviceExchangePlanned", "libsortDeviceSortDyn",
                     "libsortDebugLastDevice", "libsortDebugPoolOverlaps", "libsortDeviceExchangeCursor",
-                    "libsortDeviceTopHistogram", "libsortDeviceSplittersFromHistograms"]
+                    "libsortDeviceTopHistogram", "libsortDeviceSplittersFromHistograms", "libsortDeviceSortNoAlloc"]
 
 BOUNDS_REFERENCE = 0
 BOUNDS_EXACT = 1
@@ -108,6 +108,8 @@ def lib():
     L.libsortRankAudit.restype = ci
     L.libsortDeviceExchangePlanned.argtypes = [vp, sz, vp, ci, ci, vp, vp, sz, vp, vp, vp, sz, vp]
     L.libsortDeviceExchangePlanned.restype = ci
+    L.libsortDeviceSortNoAlloc.argtypes = [vp, vp, vp, sz, vp]
+    L.libsortDeviceSortNoAlloc.restype = ci
     L.libsortDeviceTopHistogram.argtypes = [vp, sz, vp, vp]
     L.libsortDeviceTopHistogram.restype = ci
     L.libsortDeviceSplittersFromHistograms.argtypes = [vp, ci, vp, vp, vp, vp]

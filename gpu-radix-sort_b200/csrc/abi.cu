@@ -470,6 +470,16 @@ API int libsortDeviceExchangePlanned(const uint32_t *d_in, size_t n, const uint3
                                  d_workspace, workspace_len, (cudaStream_t)stream);
 }
 
+API int libsortDeviceSortNoAlloc(const uint32_t *d_in, uint32_t *d_out, uint32_t *d_tmp, size_t n, void *stream)
+{
+    if (n > noalloc_max_keys()) {
+        fprintf(stderr, "libsortDeviceSortNoAlloc: %zu keys exceed the compiled-in maximum of %zu (LIBSORT_NOALLOC_MAX_KEYS)\n", n,
+                noalloc_max_keys());
+        return (int)cudaErrorInvalidValue;
+    }
+    return (int)sort_noalloc(d_in, d_out, d_tmp, n, (cudaStream_t)stream);
+}
+
 API int libsortDeviceTopHistogram(const uint32_t *d_in, size_t n, uint32_t *d_hist4096, void *stream)
 {
     return (int)top_histogram(d_in, n, d_hist4096, (cudaStream_t)stream);

@@ -849,4 +849,84 @@ cudaError_t step_scatter(const uint32_t *in, size_t n, uint32_t shift, uint32_t 
     return cudaGetLastError();
 }
 
+// ---- allocation-free full sort (libsortDeviceSortNoAlloc, include/libsort_b200.h) --------------
+// For callers that must not allocate (CUDA graph capture, serving loops, harnesses that forbid
+// cudaMalloc): the look-back workspace of the scatter passes lives in a file-scope device array
+// instead of caller- or pool-allocated memory.  Every GPU that loads the library holds the array
+// (about 2 MB) until exit.  The path is self-contained: the ballot-ranking kernels (architecturally
+// ordered, so no self-test and no audit), its own per-device set-up -- which only queries attributes
+// and the array's device address -- and no cudaMalloc / cudaFree / stream creation anywhere.
+// All calls share the array: it keeps the last call's contents (the words in use are cleared at the
+// start of every call, in stream order) and two calls that overlap on the GPU race.
+constexpr size_t kNoAllocMaxKeys = (size_t)1 << 22;
+constexpr size_t kNoAllocTiles = (kNoAllocMaxKeys + kTileB - 1) / kTileB;
+constexpr size_t kNoAllocWords = WS_DESC + (size_t)MAX_PASSES * kNoAllocTiles * RADIX;
+static __device__ __align__(256) uint32_t g_noalloc_scratch[kNoAllocWords];
+
+struct NoAllocDev {
+    bool ready = false;
+    int sms = 0, occ = 0, hist_occ = 0;
+    uint32_t *scratch = nullptr;  // DEVICE address of g_noalloc_scratch on this GPU (the symbol itself is a host-side stand-in)
+};
+static NoAllocDev g_noalloc_dev[64];
+static std::mutex g_noalloc_mu;
+
+static cudaError_t noalloc_setup(NoAllocDev **out)
+{
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    NoAllocDev &d = g_noalloc_dev[dev];
+    if (!d.ready) {  // once per device, with that device current
+        CK(cudaDeviceGetAttribute(&d.sms, cudaDevAttrMultiProcessorCount, dev));
+        CK(cudaFuncSetAttribute((const void *)KERNEL_B(8), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SmemB)));
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.occ, KERNEL_B(8), SORT_THREADS, sizeof(SmemB)));
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.hist_occ, k_histogram<4, HIST_THREADS, HIST_REPL>, HIST_THREADS, 0));
+        if (d.occ < 1 || d.hist_occ < 1) return cudaErrorLaunchOutOfResources;
+        void *ptr = nullptr;
+        CK(cudaGetSymbolAddress(&ptr, g_noalloc_scratch));
+        if (!ptr) return cudaErrorInvalidSymbol;
+        d.scratch = static_cast<uint32_t *>(ptr);
+        d.ready = true;
+    }
+    *out = &d;
+    return cudaSuccess;
+}
+
+size_t noalloc_max_keys() { return kNoAllocMaxKeys; }
+
+cudaError_t sort_noalloc(const uint32_t *in, uint32_t *out, uint32_t *tmp, size_t n, cudaStream_t st)
+{
+    if (n > kNoAllocMaxKeys) return cudaErrorInvalidValue;
+    if (n == 0) return cudaSuccess;
+    if (!in || !out || !tmp || tmp == out || tmp == in) return cudaErrorInvalidValue;
+    NoAllocDev *dev = nullptr;
+    CK(noalloc_setup(&dev));
+    const PassPlan plan = make_plan(0, 32);
+    const int P = plan.npass;  // 4
+    const size_t ntiles = num_tiles(n, kTileB);
+    uint32_t *ws = dev->scratch;
+    uint32_t *ghist = ws + WS_HIST, *base = ws + WS_BASE, *tickets = ws + WS_TICKET, *desc = ws + WS_DESC;
+    // histograms, tickets, skip flags and the descriptors this call uses start at zero
+    CK(cudaMemsetAsync(ws, 0, (WS_DESC + (size_t)P * ntiles * RADIX) * sizeof(uint32_t), st));
+    const size_t want = (n / 4 + HIST_THREADS * 4 - 1) / (HIST_THREADS * 4);
+    const int hgrid = (int)std::max<size_t>(1, std::min<size_t>((size_t)dev->sms * dev->hist_occ, want));
+    k_histogram<4, HIST_THREADS, HIST_REPL><<<hgrid, HIST_THREADS, 0, st>>>(in, n, plan, ghist, nullptr);
+    k_scan_hist<<<P, RADIX, 0, st>>>(ghist, base, nullptr, 0u, (uint32_t)n, tickets + SKIP_OFFSET, nullptr);
+    const int grid = (int)std::min<size_t>(ntiles, (size_t)dev->sms * dev->occ);
+    const uint32_t *src = in;
+    uint32_t *dst = tmp;  // in -> tmp -> out -> tmp -> out
+    for (int p = 0; p < P; p++) {
+        const int use_tma = (reinterpret_cast<uintptr_t>(src) & 15u) == 0;
+        const RadixBinner::Arg barg{plan.shift[p], plan.mask[p]};
+        KERNEL_B(8)<<<grid, SORT_THREADS, sizeof(SmemB), st>>>(src, dst, (uint32_t)n, barg, (const void *)(base + p * RADIX), nullptr,
+                                                               desc + (size_t)p * ntiles * RADIX, tickets + p * MAX_PORTIONS,
+                                                               (uint32_t)ntiles, use_tma, nullptr);
+        src = dst;
+        dst = dst == tmp ? out : tmp;
+    }
+    return cudaGetLastError();
+}
+
 }  // namespace b200sort

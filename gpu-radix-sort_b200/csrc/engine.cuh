@@ -113,6 +113,12 @@ cudaError_t exchange_cursor(const uint32_t *in, size_t n, const uint32_t *splitt
                             const unsigned long long *d_peer_bases, size_t cap, uint32_t *d_status, void *workspace,
                             size_t workspace_len, cudaStream_t st);
 
+// Full 32-bit sort of in[0..n) into out (tmp: n keys of scratch; in may equal out) that allocates nothing:
+// its look-back workspace is a file-scope device array in engine.cu, n <= noalloc_max_keys().  Calls
+// sharing a GPU must not overlap.  See libsortDeviceSortNoAlloc in include/libsort_b200.h.
+size_t noalloc_max_keys();
+cudaError_t sort_noalloc(const uint32_t *in, uint32_t *out, uint32_t *tmp, size_t n, cudaStream_t st);
+
 // Test hook: cap the number of tiles per look-back portion (0 = default,
 // i.e. the largest portion whose key count fits the 30-bit descriptors).
 void debug_set_portion_tiles(uint32_t tiles);

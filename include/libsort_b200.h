@@ -106,6 +106,24 @@ LIBSORT_API int libsortDeviceExchangePlanned(const uint32_t *d_in, size_t n, con
                                              uint32_t *d_status, void *d_workspace, size_t workspace_bytes,
                                              void *stream);
 /*
+ * libsortDeviceSortNoAlloc: full ascending 32-bit sort of d_in[0..n) into d_out that ALLOCATES NOTHING.
+ * It has no counterpart in the reference; it was added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  The caller passes the input, the output and n keys of scratch (d_tmp, distinct from
+ * both; d_in may equal d_out); the look-back workspace that libsortDeviceSort takes from the caller is a
+ * file-scope device array inside the library (about 2 MB, held by every GPU that loads the library until
+ * exit), hence the limit: n <= LIBSORT_NOALLOC_MAX_KEYS, larger sizes are rejected with
+ * cudaErrorInvalidValue and a message on stderr.  No cudaMalloc, cudaFree, stream creation or self-test
+ * runs on this path (it uses the ballot-ranking kernels, which need neither self-test nor audit; set-up
+ * once per device only queries attributes and the array's address).  initLibSort() is not required.
+ * Every call on a GPU shares that one array: it keeps the previous call's contents (the part a call
+ * uses is cleared at its start, in stream order), and calls that overlap on the GPU -- different streams
+ * without ordering, different host threads -- race and give wrong results; serialise them.
+ */
+#define LIBSORT_NOALLOC_MAX_KEYS ((size_t)1 << 22)
+LIBSORT_API int libsortDeviceSortNoAlloc(const uint32_t *d_in, uint32_t *d_out, uint32_t *d_tmp, size_t n, void *stream);
+
+/*
  * Splitters without a sample and without a counting pass (DistributedSorter plan="hist"):
  * libsortDeviceTopHistogram: d_hist4096[b] = keys of the shard with key >> 20 == b (zeroed first).
  * libsortDeviceSplittersFromHistograms: from the all-gathered nranks x 4096 histograms (DEVICE) ->
